@@ -1,0 +1,7 @@
+"""B200-native drop-in for the one hot path of alexeygrigorev/kubernetes-deep-learning:
+gateway preprocessing (model_server.py:18,53) + the clothing-model Xception-299 forward that
+TF-Serving runs behind model_server.py:55.  Host code is Python calling a C-ABI CUDA library
+(include/kdl.h, csrc/); there is no CPU fallback."""
+from . import arch, weights  # noqa: F401
+
+__all__ = ["arch", "weights"]

@@ -1,0 +1,108 @@
+"""CPU tests of the network oracle and of the architecture/weight spec (structural known answers,
+SURVEY.md §8c (ii), and the regression pins in tests/golden/xception_golden.npz).
+The network is PARITY UNPINNED against the reference (TF 2.3.0 + the .h5 are unreachable)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import kdl_b200  # noqa: F401
+from kdl_b200 import arch, weights
+from oracle import xception_oracle as xo
+
+
+def test_structural_known_answers():
+    assert arch.param_count(base_only=True) == 20_861_480      # Keras no-top Xception
+    assert arch.param_count() == 21_067_390
+    assert arch.mac_count(299) == 8_355_561_296
+    assert arch.mac_count(150) == 1_924_603_256
+    assert arch.spatial_chain(299) == [299, 149, 147, 74, 37, 19, 10]
+    assert arch.spatial_chain(150) == [150, 74, 72, 36, 18, 9, 5]
+
+
+def test_blob_roundtrip():
+    W = weights.make_weights(1, "calibrated")
+    blob = weights.pack_blob(W)
+    assert blob.dtype == np.float32 and blob.size == 21_067_390
+    W2 = weights.unpack_blob(blob)
+    assert all(np.array_equal(W[k], W2[k]) for k in W)
+    with pytest.raises(ValueError):
+        weights.unpack_blob(blob[:-1])
+
+
+def test_weights_deterministic():
+    a = weights.make_weights(1, "calibrated")
+    b = weights.make_weights(1, "calibrated")
+    c = weights.make_weights(2, "calibrated")
+    assert all(np.array_equal(a[k], b[k]) for k in a)
+    assert not np.array_equal(a["block1_conv1/kernel"], c["block1_conv1/kernel"])
+
+
+def _inputs(h, n=2):
+    rng = np.random.default_rng(0)
+    u = rng.integers(0, 256, (n, h, h, 3), dtype=np.uint8)
+    x = u.astype(np.float32)
+    x /= 127.5
+    x -= 1.0
+    return x
+
+
+@pytest.mark.parametrize("h", [299, 150])
+@pytest.mark.parametrize("init", ["keras_default", "calibrated"])
+def test_regression_pins_and_fp32_tolerance(golden_dir, h, init):
+    g = np.load(os.path.join(golden_dir, "xception_golden.npz"))
+    W = weights.make_weights(1, init)
+    x = _inputs(h)
+    taps = {}
+    y64 = xo.forward(W, x, torch.float64, taps)
+    assert y64.shape == (2, 10)
+    assert xo.rel_err(y64, g[f"logits_{h}_{init}"]) < 1e-9
+    for k, v in taps.items():
+        want = g[f"tapstat_{h}_{init}_{k}"]
+        got = np.array([np.abs(v).mean(), v.mean(), v.reshape(-1)[:4].sum()])
+        np.testing.assert_allclose(got, want, rtol=1e-7, atol=1e-12, err_msg=k)
+    # north_star: fp32 path within 1e-4 relative of truth
+    y32 = xo.forward(W, x, torch.float32)
+    for i in range(2):
+        assert xo.rel_err(y32[i], y64[i]) < 1e-4
+    chain = arch.spatial_chain(h)
+    assert taps["block1_conv1_act"].shape == (2, chain[1], chain[1], 32)
+    assert taps["block2_out"].shape == (2, chain[3], chain[3], 128)
+    assert taps["block12_out"].shape == (2, chain[5], chain[5], 728)
+    assert taps["block14_sepconv2_act"].shape == (2, chain[6], chain[6], 2048)
+
+
+def test_tf_same_maxpool_padding_rule():
+    """even input pads (0,1); odd pads (1,1); a symmetric pad=1 is a different op."""
+    x = torch.arange(36, dtype=torch.float64).reshape(1, 1, 6, 6)
+    y = xo._maxpool_same(x)
+    assert y.shape[-1] == 3
+    # window 0 covers rows/cols 0..2 (no leading pad) -> max is element (2,2) = 14
+    assert y[0, 0, 0, 0].item() == 14.0
+    sym = torch.nn.functional.max_pool2d(x, 3, 2, padding=1)
+    assert sym[0, 0, 0, 0].item() == 7.0  # the silent-error variant
+    x = torch.arange(49, dtype=torch.float64).reshape(1, 1, 7, 7)
+    assert xo._maxpool_same(x).shape[-1] == 4
+    assert xo._maxpool_same(x)[0, 0, 0, 0].item() == 8.0
+
+
+def test_calibrated_init_is_not_blind():
+    """with the calibrated init every middle-flow branch matters."""
+    W = weights.make_weights(1, "calibrated")
+    taps = {}
+    xo.forward(W, _inputs(150, 1), torch.float64, taps)
+    br = np.abs(taps["block8_sepconv3_bn"]).mean()
+    skip = np.abs(taps["block7_out"]).mean()
+    assert 0.1 < br / skip < 10.0
+    W["block8_sepconv2/pointwise_kernel"] = W["block8_sepconv2/pointwise_kernel"] * 0
+    y0 = xo.forward(weights.make_weights(1, "calibrated"), _inputs(150, 1), torch.float64)
+    y1 = xo.forward(W, _inputs(150, 1), torch.float64)
+    assert xo.rel_err(y1, y0) > 1e-3
+
+
+def test_head_inner_zero_variant():
+    W = weights.make_weights(1, "calibrated", head_inner=0)
+    assert "dense_inner/kernel" not in W and W["dense_7/kernel"].shape == (2048, 10)
+    y = xo.forward(W, _inputs(150, 1), torch.float32)
+    assert y.shape == (1, 10)
