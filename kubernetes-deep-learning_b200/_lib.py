@@ -1,0 +1,78 @@
+"""ctypes binding of include/kdl.h.  Loading fails loudly when the CUDA library is missing: there is no
+CPU fallback anywhere in this package."""
+import ctypes
+import os
+from ctypes import POINTER, c_char_p, c_float, c_int32, c_int64, c_size_t, c_void_p
+
+_CSRC = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc")
+LIB_PATH = os.path.join(_CSRC, "libkdl.so")
+
+KDL_OK, KDL_EINVAL, KDL_ECUDA, KDL_ESTATE, KDL_ENOMEM = 0, -1, -2, -3, -4
+PRECISION_F32, PRECISION_BF16 = 0, 1
+GEMM_AUTO, GEMM_SIMPLE = 0, 1
+
+# every symbol include/kdl.h declares
+SYMBOLS = [
+    "kdl_create", "kdl_destroy", "kdl_last_error", "kdl_weight_count", "kdl_load_weights",
+    "kdl_preprocess_u8", "kdl_forward", "kdl_predict_u8", "kdl_predict_u8_host", "kdl_forward_host",
+    "kdl_num_taps", "kdl_tap_name", "kdl_layer_output", "kdl_last_launch_count", "kdl_gemm_bf16",
+    "kdl_version",
+]
+
+
+class KdlConfig(ctypes.Structure):
+    _fields_ = [("device", c_int32), ("max_batch", c_int32), ("input_size", c_int32), ("head_inner", c_int32),
+                ("precision", c_int32), ("gemm_impl", c_int32), ("keep_taps", c_int32), ("reserved", c_int32)]
+
+
+class KdlError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"kdl error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def load():
+    """Returns the loaded library; raises if libkdl.so has not been built (run __graft_entry__.build())."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a).  This package has no CPU fallback.")
+    lib = ctypes.CDLL(LIB_PATH)
+    P = c_void_p
+    lib.kdl_create.argtypes = [POINTER(KdlConfig), POINTER(P)]
+    lib.kdl_destroy.argtypes = [P]
+    lib.kdl_last_error.argtypes = [P]
+    lib.kdl_last_error.restype = c_char_p
+    lib.kdl_weight_count.argtypes = [c_int32]
+    lib.kdl_weight_count.restype = c_size_t
+    lib.kdl_load_weights.argtypes = [P, P, c_size_t]
+    lib.kdl_preprocess_u8.argtypes = [P, P, P, P, P, P, c_int32, P, P]
+    lib.kdl_forward.argtypes = [P, P, c_int32, P, P]
+    lib.kdl_predict_u8.argtypes = [P, P, P, P, P, P, c_int32, P, P]
+    lib.kdl_predict_u8_host.argtypes = [P, P, c_size_t, P, P, P, P, c_int32, P]
+    lib.kdl_forward_host.argtypes = [P, P, c_int32, P]
+    lib.kdl_num_taps.argtypes = [P]
+    lib.kdl_tap_name.argtypes = [P, c_int32]
+    lib.kdl_tap_name.restype = c_char_p
+    lib.kdl_layer_output.argtypes = [P, c_char_p, P, c_size_t, POINTER(c_int32 * 4), POINTER(c_int32), P]
+    lib.kdl_last_launch_count.argtypes = [P]
+    lib.kdl_gemm_bf16.argtypes = [P, P, P, P, P, c_int32, c_int32, c_int32, c_int32, P]
+    lib.kdl_version.restype = c_char_p
+    for s in SYMBOLS:
+        fn = getattr(lib, s)
+        if fn.restype is ctypes.c_int:
+            fn.restype = c_int32
+    _lib = lib
+    return lib
+
+
+def check(rc, handle=None):
+    if rc != KDL_OK:
+        msg = load().kdl_last_error(handle)
+        raise KdlError(rc, msg.decode() if msg else "?")

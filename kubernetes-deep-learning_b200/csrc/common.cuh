@@ -1,0 +1,68 @@
+// Shared device helpers for the kdl kernels (sm_100a).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace kdl {
+
+typedef __nv_bfloat16 bf16;
+
+// ---- 4-channel vector access, storage type T in {float, bf16}; math is always fp32 ----
+template <typename T> struct V4;
+
+template <> struct V4<float> {
+    static __device__ __forceinline__ float4 ld(const float *p) { return *reinterpret_cast<const float4 *>(p); }
+    static __device__ __forceinline__ void st(float *p, float4 v) { *reinterpret_cast<float4 *>(p) = v; }
+};
+
+template <> struct V4<bf16> {
+    static __device__ __forceinline__ float4 ld(const bf16 *p) {
+        uint2 r = *reinterpret_cast<const uint2 *>(p);
+        float4 v;
+        v.x = __uint_as_float(r.x << 16);
+        v.y = __uint_as_float(r.x & 0xffff0000u);
+        v.z = __uint_as_float(r.y << 16);
+        v.w = __uint_as_float(r.y & 0xffff0000u);
+        return v;
+    }
+    static __device__ __forceinline__ void st(bf16 *p, float4 v) {
+        __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y);
+        __nv_bfloat162 b = __floats2bfloat162_rn(v.z, v.w);
+        uint2 r;
+        r.x = *reinterpret_cast<uint32_t *>(&a);
+        r.y = *reinterpret_cast<uint32_t *>(&b);
+        *reinterpret_cast<uint2 *>(p) = r;
+    }
+};
+
+template <typename T> __device__ __forceinline__ float ld1(const T *p);
+template <> __device__ __forceinline__ float ld1<float>(const float *p) { return *p; }
+template <> __device__ __forceinline__ float ld1<bf16>(const bf16 *p) { return __bfloat162float(*p); }
+template <typename T> __device__ __forceinline__ void st1(T *p, float v);
+template <> __device__ __forceinline__ void st1<float>(float *p, float v) { *p = v; }
+template <> __device__ __forceinline__ void st1<bf16>(bf16 *p, float v) { *p = __float2bfloat16_rn(v); }
+
+__device__ __forceinline__ float4 relu4(float4 v) {
+    return make_float4(fmaxf(v.x, 0.f), fmaxf(v.y, 0.f), fmaxf(v.z, 0.f), fmaxf(v.w, 0.f));
+}
+__device__ __forceinline__ float4 fma4(float4 a, float4 w, float4 acc) {
+    acc.x = fmaf(a.x, w.x, acc.x);
+    acc.y = fmaf(a.y, w.y, acc.y);
+    acc.z = fmaf(a.z, w.z, acc.z);
+    acc.w = fmaf(a.w, w.w, acc.w);
+    return acc;
+}
+__device__ __forceinline__ float4 max4(float4 a, float4 b) {
+    return make_float4(fmaxf(a.x, b.x), fmaxf(a.y, b.y), fmaxf(a.z, b.z), fmaxf(a.w, b.w));
+}
+__device__ __forceinline__ float4 add4(float4 a, float4 b) {
+    return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+}
+
+// The gateway's scaling, bit-exact: np.float32 x /= 127.5 ; x -= 1.0  (two roundings, no FMA contraction).
+__device__ __forceinline__ float scale_px(uint8_t v) {
+    return __fsub_rn(__fdiv_rn((float)v, 127.5f), 1.0f);
+}
+
+}  // namespace kdl

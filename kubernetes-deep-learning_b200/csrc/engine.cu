@@ -1,0 +1,757 @@
+// kdl engine: the C ABI of include/kdl.h on top of the kernels in kernels.cuh / gemm_tc.cuh.
+// One KdlModel = one GPU replica of the clothing-model graph (convert.py:4-6) with its weights folded and
+// resident, an activation arena sized for max_batch, and the kernel launch sequence of the forward pass that
+// TF-Serving would run for model_server.py:55.
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/kdl.h"
+#include "gemm_tc.cuh"
+#include "kernels.cuh"
+
+using namespace kdl;
+
+static thread_local char g_err[512] = "";
+
+static void set_err(char *dst, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(dst, 512, fmt, ap);
+    va_end(ap);
+    if (dst != g_err) { strncpy(g_err, dst, 511); g_err[511] = 0; }
+}
+
+#define CK(call)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t e_ = (call);                                                                         \
+        if (e_ != cudaSuccess) {                                                                         \
+            set_err(err, "%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_));           \
+            return KDL_ECUDA;                                                                            \
+        }                                                                                                \
+    } while (0)
+
+static const float BN_EPS = 1e-3f;  // Keras BatchNormalization(epsilon=1e-3) used by applications.Xception
+
+static inline int conv_valid(int n, int k, int s) { return (n - k) / s + 1; }
+static inline int same_out(int n, int s) { return (n + s - 1) / s; }
+
+// ---------------------------------------------------------------------------------------------------
+// canonical weight order (mirror of kubernetes-deep-learning_b200/arch.py weight_spec)
+// ---------------------------------------------------------------------------------------------------
+struct SepSpec { int block, idx, cin, cout; };
+
+static std::vector<SepSpec> sep_specs() {
+    std::vector<SepSpec> v;
+    v.push_back({2, 1, 64, 128}); v.push_back({2, 2, 128, 128});
+    v.push_back({3, 1, 128, 256}); v.push_back({3, 2, 256, 256});
+    v.push_back({4, 1, 256, 728}); v.push_back({4, 2, 728, 728});
+    for (int b = 5; b <= 12; ++b) for (int j = 1; j <= 3; ++j) v.push_back({b, j, 728, 728});
+    v.push_back({13, 1, 728, 728}); v.push_back({13, 2, 728, 1024});
+    v.push_back({14, 1, 1024, 1536}); v.push_back({14, 2, 1536, 2048});
+    return v;
+}
+struct ResSpec { int block, cin, cout; };
+static const ResSpec RES_SPECS[4] = {{2, 64, 128}, {3, 128, 256}, {4, 256, 728}, {13, 728, 1024}};
+
+extern "C" size_t kdl_weight_count(int32_t head_inner) {
+    size_t n = 27 * 32 + 4 * 32 + 288 * 64 + 4 * 64;
+    for (auto &r : RES_SPECS) n += (size_t)r.cin * r.cout + 4 * r.cout;
+    for (auto &s : sep_specs()) n += 9 * (size_t)s.cin + (size_t)s.cin * s.cout + 4 * s.cout;
+    if (head_inner > 0) n += 2048 * (size_t)head_inner + head_inner + (size_t)head_inner * 10 + 10;
+    else n += 2048 * 10 + 10;
+    return n;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// model
+// ---------------------------------------------------------------------------------------------------
+struct GemmW {
+    int K = 0, N = 0;
+    void *Wkn = nullptr;   // storage T, [K][N]  (CUDA-core GEMM)
+    bf16 *Wnk = nullptr;   // bf16, [N][K]       (tcgen05 GEMM, K-major B operand)
+    float *bias = nullptr; // folded BN shift
+    CUtensorMap tmB;       // TMA descriptor of Wnk
+};
+
+struct Tap {
+    std::string name;
+    int relu_applied;
+    int H, C;          // spatial side (1 for vectors) and channels
+    void *buf = nullptr;  // storage T (or float for vectors), sized max_batch
+    bool is_float;
+};
+
+struct KdlModel {
+    KdlConfig cfg;
+    char err[512];
+    bool weights_loaded = false;
+    int launches = 0;
+    int last_B = 0;
+    int sp[7];  // spatial chain S,H1..H6
+    size_t esz; // storage element size
+
+    // weights
+    float *w_conv1 = nullptr, *b_conv1 = nullptr;
+    GemmW conv2, res[4];
+    std::vector<float *> dw;      // [34] [9][C]
+    std::vector<GemmW> pw;        // [34]
+    float *W1 = nullptr, *b1 = nullptr, *W2 = nullptr, *b2 = nullptr;
+    std::vector<void *> owned;    // every device allocation (freed in destroy)
+
+    // arena
+    void *X = nullptr, *T = nullptr, *U = nullptr, *R = nullptr, *S = nullptr;
+    uint8_t *u8img = nullptr;     // resized uint8 batch (fused path)
+    uint8_t *d_src = nullptr;     // staging for *_host calls
+    size_t d_src_cap = 0;
+    float *d_in_f32 = nullptr;    // staging for kdl_forward_host
+    float *d_logits = nullptr;
+    ImgMeta *d_meta = nullptr;
+    int32_t *d_xtab = nullptr, *d_ytab = nullptr;
+    static const int NSLOT = 4;
+    ImgMeta *h_meta[NSLOT] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t slot_ev[NSLOT];
+    int slot = 0;
+    cudaStream_t own_stream = nullptr;
+
+    // TMA descriptors of the activation buffers viewed as [rows, K] matrices are built per call site
+    std::vector<Tap> taps;
+    tc::TmaEncoder tma;
+};
+
+template <typename T> struct Runner;
+
+static int dev_alloc(KdlModel *m, void **p, size_t bytes) {
+    char *err = m->err;
+    CK(cudaMalloc(p, bytes ? bytes : 16));
+    m->owned.push_back(*p);
+    return KDL_OK;
+}
+
+#define LAUNCH_CHECK()                                                    \
+    do {                                                                  \
+        m->launches++;                                                    \
+        cudaError_t e_ = cudaGetLastError();                              \
+        if (e_ != cudaSuccess) {                                          \
+            set_err(m->err, "%s:%d launch failed: %s", __FILE__, __LINE__, cudaGetErrorString(e_)); \
+            return KDL_ECUDA;                                             \
+        }                                                                 \
+    } while (0)
+
+static int find_tap(KdlModel *m, const char *name) {
+    for (size_t i = 0; i < m->taps.size(); ++i)
+        if (m->taps[i].name == name) return (int)i;
+    return -1;
+}
+
+template <typename T> struct Runner {
+    KdlModel *m;
+    cudaStream_t st;
+    int B;
+
+    int tap(const char *name, const void *src, int H, int C, int relu_applied, bool is_float = false) {
+        if (!m->cfg.keep_taps) return KDL_OK;
+        char *err = m->err;
+        int i = find_tap(m, name);
+        if (i < 0) {
+            Tap t;
+            t.name = name; t.relu_applied = relu_applied; t.H = H; t.C = C; t.is_float = is_float;
+            size_t bytes = (size_t)m->cfg.max_batch * H * H * C * (is_float ? 4 : sizeof(T));
+            CK(cudaMalloc(&t.buf, bytes));
+            m->owned.push_back(t.buf);
+            m->taps.push_back(t);
+            i = (int)m->taps.size() - 1;
+        }
+        size_t bytes = (size_t)B * H * H * C * (is_float ? 4 : sizeof(T));
+        CK(cudaMemcpyAsync(m->taps[i].buf, src, bytes, cudaMemcpyDeviceToDevice, st));
+        return KDL_OK;
+    }
+
+    int dwconv(const T *in, const float *w, T *out, int H, int C, int relu_in) {
+        int rows = H >= 64 ? 8 : (H >= 16 ? 5 : H);
+        int vec = H * (C / 4);
+        dim3 grid((vec + 127) / 128, (H + rows - 1) / rows, B);
+        k_dw3x3<T><<<grid, 128, 0, st>>>(in, w, out, H, H, C, relu_in, rows);
+        LAUNCH_CHECK();
+        return KDL_OK;
+    }
+
+    bool use_tc() const {
+        return sizeof(T) == 2 && m->cfg.gemm_impl == KDL_GEMM_AUTO;
+    }
+
+    // out[M,N] = act(A*W + bias) (+res).  A rows through RowMap (mode 0 = dense).
+    int gemm(const T *A, const GemmW &g, const T *resid, T *out, int M, int relu, RowMap rm) {
+        if (use_tc() && rm.mode == 0 && tc::shape_supported(M, g.N, g.K)) {
+            int rc = tc::launch_gemm(m->tma, (const bf16 *)A, g.Wnk, &g.tmB, g.bias, (const bf16 *)resid, (bf16 *)out,
+                                     M, g.N, g.K, relu, st, m->err);
+            if (rc != KDL_OK) return rc;
+            m->launches++;
+            return KDL_OK;
+        }
+        dim3 grid((g.N + GS_BN - 1) / GS_BN, (M + GS_BM - 1) / GS_BM);
+        k_gemm_simple<T><<<grid, 256, 0, st>>>(A, (const T *)g.Wkn, g.bias, resid, out, M, g.N, g.K, relu, rm);
+        LAUNCH_CHECK();
+        return KDL_OK;
+    }
+
+    // Conv2D(1x1, strides 2, 'same') + BN : residual projection.  in: [B,H,H,Cin] -> out [B,Ho,Ho,Cout]
+    int projection(const T *in, const GemmW &g, T *out, int H, int Ho) {
+        int M = B * Ho * Ho;
+        if (use_tc() && tc::shape_supported(M, g.N, g.K)) {
+            long long total = (long long)M * (g.K / 4);
+            k_subsample2<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(in, (T *)m->S, B, H, H, g.K, Ho, Ho);
+            LAUNCH_CHECK();
+            return gemm((const T *)m->S, g, nullptr, out, M, 0, RowMap{0, 0, 0, 0, 0, 0});
+        }
+        return gemm(in, g, nullptr, out, M, 0, RowMap{1, H, H, Ho, Ho, g.K});
+    }
+
+    int pool_add(const T *in, const T *resid, T *out, int H, int C, int Ho) {
+        int pad_total = (Ho - 1) * 2 + 3 - H;
+        if (pad_total < 0) pad_total = 0;
+        int pad_lo = pad_total / 2;  // TF SAME: extra padding goes to the end
+        long long total = (long long)B * Ho * Ho * (C / 4);
+        k_maxpool_add<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(in, resid, out, B, H, H, C, Ho, Ho, pad_lo);
+        LAUNCH_CHECK();
+        return KDL_OK;
+    }
+
+#define RUN(x)                          \
+    do {                                \
+        int rc_ = (x);                  \
+        if (rc_ != KDL_OK) return rc_;  \
+    } while (0)
+
+    // in_f32: serving_default tensor, or in_u8: resized uint8 batch (exactly one non-null)
+    int forward(const float *in_f32, const uint8_t *in_u8, float *d_logits) {
+        const int *sp = m->sp;
+        T *X = (T *)m->X, *Tb = (T *)m->T, *U = (T *)m->U, *R = (T *)m->R;
+        const RowMap dense{0, 0, 0, 0, 0, 0};
+        char name[64];
+        // ---- block1 ----
+        {
+            long long threads = (long long)B * sp[1] * sp[1] * 4;
+            unsigned grid = (unsigned)((threads + 255) / 256);
+            if (in_f32) k_conv1<float, T><<<grid, 256, 0, st>>>(in_f32, m->w_conv1, m->b_conv1, U, B, sp[0], sp[1]);
+            else k_conv1<uint8_t, T><<<grid, 256, 0, st>>>(in_u8, m->w_conv1, m->b_conv1, U, B, sp[0], sp[1]);
+            LAUNCH_CHECK();
+            RUN(tap("block1_conv1_act", U, sp[1], 32, 1));
+            // block1_conv2 as an implicit GEMM (K = 288)
+            RUN(gemm(U, m->conv2, nullptr, X, B * sp[2] * sp[2], 1, RowMap{2, sp[1], sp[1], sp[2], sp[2], 32}));
+            RUN(tap("block1_conv2_act", X, sp[2], 64, 1));
+        }
+        // ---- entry/exit blocks with projection + pool: 2,3,4 then middle, then 13 ----
+        int si = 0;  // sepconv index
+        auto entry_block = [&](int blk, int ri, int H, int Ho) -> int {
+            const GemmW &rg = m->res[ri];
+            RUN(projection(X, rg, R, H, Ho));
+            snprintf(name, sizeof name, "block%d_res_bn", blk);
+            RUN(tap(name, R, Ho, rg.N, 0));
+            // sepconv1: ReLU on load except block2 (input is already post-ReLU there)
+            RUN(dwconv(X, m->dw[si], Tb, H, m->pw[si].K, blk != 2));
+            RUN(gemm(Tb, m->pw[si], nullptr, U, B * H * H, 1, dense));  // next sepconv's ReLU folded here
+            snprintf(name, sizeof name, "block%d_sepconv1_bn", blk);
+            RUN(tap(name, U, H, m->pw[si].N, 1));
+            ++si;
+            RUN(dwconv(U, m->dw[si], Tb, H, m->pw[si].K, 0));
+            RUN(gemm(Tb, m->pw[si], nullptr, U, B * H * H, 0, dense));
+            snprintf(name, sizeof name, "block%d_sepconv2_bn", blk);
+            RUN(tap(name, U, H, m->pw[si].N, 0));
+            int C = m->pw[si].N;
+            ++si;
+            RUN(pool_add(U, R, X, H, C, Ho));
+            snprintf(name, sizeof name, "block%d_out", blk);
+            RUN(tap(name, X, Ho, C, 0));
+            return KDL_OK;
+        };
+        RUN(entry_block(2, 0, sp[2], sp[3]));
+        RUN(entry_block(3, 1, sp[3], sp[4]));
+        RUN(entry_block(4, 2, sp[4], sp[5]));
+        // ---- middle flow ----
+        {
+            const int H = sp[5], M = B * H * H;
+            for (int blk = 5; blk <= 12; ++blk) {
+                RUN(dwconv(X, m->dw[si], Tb, H, 728, 1));
+                RUN(gemm(Tb, m->pw[si], nullptr, U, M, 1, dense));
+                snprintf(name, sizeof name, "block%d_sepconv1_bn", blk);
+                RUN(tap(name, U, H, 728, 1));
+                ++si;
+                RUN(dwconv(U, m->dw[si], Tb, H, 728, 0));
+                RUN(gemm(Tb, m->pw[si], nullptr, U, M, 1, dense));
+                snprintf(name, sizeof name, "block%d_sepconv2_bn", blk);
+                RUN(tap(name, U, H, 728, 1));
+                ++si;
+                RUN(dwconv(U, m->dw[si], Tb, H, 728, 0));
+                RUN(gemm(Tb, m->pw[si], X, X, M, 0, dense));  // + residual, in place on the skip tensor
+                ++si;
+                snprintf(name, sizeof name, "block%d_out", blk);
+                RUN(tap(name, X, H, 728, 0));
+            }
+        }
+        RUN(entry_block(13, 3, sp[5], sp[6]));
+        // ---- block14: ReLU after BN ----
+        {
+            const int H = sp[6], M = B * H * H;
+            RUN(dwconv(X, m->dw[si], Tb, H, 1024, 0));
+            RUN(gemm(Tb, m->pw[si], nullptr, U, M, 1, dense));
+            RUN(tap("block14_sepconv1_act", U, H, 1536, 1));
+            ++si;
+            RUN(dwconv(U, m->dw[si], Tb, H, 1536, 0));
+            RUN(gemm(Tb, m->pw[si], nullptr, U, M, 1, dense));
+            RUN(tap("block14_sepconv2_act", U, H, 2048, 1));
+            ++si;
+        }
+        // ---- head ----
+        {
+            const int H = sp[6];
+            float *feat = nullptr;
+            if (m->cfg.keep_taps) {
+                int i = find_tap(m, "avg_pool");
+                if (i < 0) {
+                    RUN(tap("avg_pool", m->d_logits, 1, 2048, 0, true));  // allocates; content overwritten below
+                    i = find_tap(m, "avg_pool");
+                }
+                feat = (float *)m->taps[i].buf;
+            }
+            size_t smem = (2048 + 8 * 128 + 128) * sizeof(float);
+            k_gap_head<T><<<B, 256, smem, st>>>(U, H * H, 2048, m->W1, m->b1, m->cfg.head_inner, m->W2, m->b2, 10,
+                                                feat, d_logits);
+            LAUNCH_CHECK();
+        }
+        return KDL_OK;
+    }
+};
+
+// ---------------------------------------------------------------------------------------------------
+// weight loading: fold BN, pack, upload
+// ---------------------------------------------------------------------------------------------------
+static inline uint16_t f2bf(float f) {
+    uint32_t u;
+    memcpy(&u, &f, 4);
+    if ((u & 0x7fffffffu) > 0x7f800000u) return (uint16_t)((u >> 16) | 0x40);
+    u += 0x7fffu + ((u >> 16) & 1u);  // round to nearest even
+    return (uint16_t)(u >> 16);
+}
+
+struct BnFold { std::vector<float> scale, shift; };
+
+static BnFold fold_bn(const float *&p, int c) {
+    const float *g = p, *be = p + c, *mu = p + 2 * c, *var = p + 3 * c;
+    p += 4 * (size_t)c;
+    BnFold f;
+    f.scale.resize(c); f.shift.resize(c);
+    for (int i = 0; i < c; ++i) {
+        double s = (double)g[i] / sqrt((double)var[i] + (double)BN_EPS);
+        f.scale[i] = (float)s;
+        f.shift[i] = (float)((double)be[i] - (double)mu[i] * s);
+    }
+    return f;
+}
+
+static int upload(KdlModel *m, void **dst, const void *src, size_t bytes) {
+    char *err = m->err;
+    int rc = dev_alloc(m, dst, bytes);
+    if (rc) return rc;
+    CK(cudaMemcpy(*dst, src, bytes, cudaMemcpyHostToDevice));
+    return KDL_OK;
+}
+
+// kernel [K][N] fp32 (Keras (kh,kw,cin,cout) flattened) + BN -> GemmW
+static int make_gemm(KdlModel *m, GemmW &g, const float *kern, int K, int N, const BnFold *bn, const float *bias) {
+    g.K = K; g.N = N;
+    std::vector<float> w((size_t)K * N);
+    for (int k = 0; k < K; ++k)
+        for (int n = 0; n < N; ++n) w[(size_t)k * N + n] = kern[(size_t)k * N + n] * (bn ? bn->scale[n] : 1.f);
+    std::vector<float> b(N);
+    for (int n = 0; n < N; ++n) b[n] = bn ? bn->shift[n] : (bias ? bias[n] : 0.f);
+    int rc = upload(m, (void **)&g.bias, b.data(), N * sizeof(float));
+    if (rc) return rc;
+    if (m->cfg.precision == KDL_PRECISION_F32) {
+        return upload(m, &g.Wkn, w.data(), w.size() * sizeof(float));
+    }
+    std::vector<uint16_t> wkn((size_t)K * N), wnk((size_t)K * N);
+    for (int k = 0; k < K; ++k)
+        for (int n = 0; n < N; ++n) {
+            uint16_t v = f2bf(w[(size_t)k * N + n]);
+            wkn[(size_t)k * N + n] = v;
+            wnk[(size_t)n * K + k] = v;
+        }
+    rc = upload(m, &g.Wkn, wkn.data(), wkn.size() * 2);
+    if (rc) return rc;
+    rc = upload(m, (void **)&g.Wnk, wnk.data(), wnk.size() * 2);
+    if (rc) return rc;
+    if (m->tma.ok()) {
+        if (!m->tma.encode_2d(&g.tmB, g.Wnk, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, tc::BLOCK_K, tc::BLOCK_N)) {
+            set_err(m->err, "cuTensorMapEncodeTiled failed for weight [%d,%d]", N, K);
+            return KDL_ECUDA;
+        }
+    }
+    return KDL_OK;
+}
+
+extern "C" int kdl_load_weights(KdlModel *m, const float *blob, size_t n_floats) {
+    if (!m || !blob) { set_err(g_err, "kdl_load_weights: null argument"); return KDL_EINVAL; }
+    char *err = m->err;
+    if (m->weights_loaded) { set_err(err, "kdl_load_weights: weights already loaded"); return KDL_ESTATE; }
+    size_t want = kdl_weight_count(m->cfg.head_inner);
+    if (n_floats != want) {
+        set_err(err, "kdl_load_weights: blob has %zu floats, head_inner=%d needs %zu", n_floats, m->cfg.head_inner, want);
+        return KDL_EINVAL;
+    }
+    CK(cudaSetDevice(m->cfg.device));
+    const float *p = blob;
+    int rc;
+    // block1_conv1 (3,3,3,32) + bn : CUDA-core kernel, fp32 weights [27][32]
+    {
+        const float *k = p; p += 27 * 32;
+        BnFold f = fold_bn(p, 32);
+        std::vector<float> w(27 * 32);
+        for (int i = 0; i < 27; ++i) for (int c = 0; c < 32; ++c) w[i * 32 + c] = k[i * 32 + c] * f.scale[c];
+        if ((rc = upload(m, (void **)&m->w_conv1, w.data(), w.size() * 4))) return rc;
+        if ((rc = upload(m, (void **)&m->b_conv1, f.shift.data(), 32 * 4))) return rc;
+    }
+    {
+        const float *k = p; p += 288 * 64;
+        BnFold f = fold_bn(p, 64);
+        if ((rc = make_gemm(m, m->conv2, k, 288, 64, &f, nullptr))) return rc;
+    }
+    auto seps = sep_specs();
+    m->dw.assign(seps.size(), nullptr);
+    m->pw.assign(seps.size(), GemmW());
+    size_t si = 0;
+    auto load_sep = [&](const SepSpec &s) -> int {
+        const float *dwk = p; p += 9 * (size_t)s.cin;
+        const float *pwk = p; p += (size_t)s.cin * s.cout;
+        BnFold f = fold_bn(p, s.cout);
+        int r = upload(m, (void **)&m->dw[si], dwk, 9 * (size_t)s.cin * 4);
+        if (r) return r;
+        r = make_gemm(m, m->pw[si], pwk, s.cin, s.cout, &f, nullptr);
+        ++si;
+        return r;
+    };
+    auto load_res = [&](int ri) -> int {
+        const ResSpec &r = RES_SPECS[ri];
+        const float *k = p; p += (size_t)r.cin * r.cout;
+        BnFold f = fold_bn(p, r.cout);
+        return make_gemm(m, m->res[ri], k, r.cin, r.cout, &f, nullptr);
+    };
+    for (int ri = 0; ri < 3; ++ri) {
+        if ((rc = load_res(ri))) return rc;
+        if ((rc = load_sep(seps[si]))) return rc;
+        if ((rc = load_sep(seps[si]))) return rc;
+    }
+    for (int i = 0; i < 24; ++i)
+        if ((rc = load_sep(seps[si]))) return rc;
+    if ((rc = load_res(3))) return rc;
+    for (int i = 0; i < 4; ++i)
+        if ((rc = load_sep(seps[si]))) return rc;
+    int hi = m->cfg.head_inner;
+    if (hi > 0) {
+        if ((rc = upload(m, (void **)&m->W1, p, 2048 * (size_t)hi * 4))) return rc; p += 2048 * (size_t)hi;
+        if ((rc = upload(m, (void **)&m->b1, p, hi * 4))) return rc; p += hi;
+        if ((rc = upload(m, (void **)&m->W2, p, (size_t)hi * 10 * 4))) return rc; p += (size_t)hi * 10;
+    } else {
+        if ((rc = upload(m, (void **)&m->W2, p, 2048 * 10 * 4))) return rc; p += 2048 * 10;
+    }
+    if ((rc = upload(m, (void **)&m->b2, p, 10 * 4))) return rc; p += 10;
+    if ((size_t)(p - blob) != want) { set_err(err, "internal: weight cursor mismatch"); return KDL_EINVAL; }
+    m->weights_loaded = true;
+    return KDL_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// lifecycle
+// ---------------------------------------------------------------------------------------------------
+extern "C" int kdl_create(const KdlConfig *cfg, KdlModel **out) {
+    char *err = g_err;
+    if (!cfg || !out) { set_err(g_err, "kdl_create: null argument"); return KDL_EINVAL; }
+    if (cfg->max_batch < 1 || cfg->input_size < 71 || cfg->input_size > 1024 || cfg->head_inner < 0 ||
+        cfg->head_inner > 128 || (cfg->precision != KDL_PRECISION_F32 && cfg->precision != KDL_PRECISION_BF16)) {
+        set_err(g_err, "kdl_create: bad config (max_batch=%d input_size=%d head_inner=%d precision=%d)",
+                cfg->max_batch, cfg->input_size, cfg->head_inner, cfg->precision);
+        return KDL_EINVAL;
+    }
+    int ndev = 0;
+    CK(cudaGetDeviceCount(&ndev));
+    if (cfg->device < 0 || cfg->device >= ndev) {
+        set_err(g_err, "kdl_create: device %d not present (%d CUDA devices)", cfg->device, ndev);
+        return KDL_EINVAL;
+    }
+    CK(cudaSetDevice(cfg->device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, cfg->device));
+    if (prop.major != 10) {
+        set_err(g_err, "kdl_create: device %d is sm_%d%d; this library is built for sm_100a (B200) only",
+                cfg->device, prop.major, prop.minor);
+        return KDL_ECUDA;
+    }
+    KdlModel *m = new (std::nothrow) KdlModel();
+    if (!m) { set_err(g_err, "kdl_create: out of host memory"); return KDL_ENOMEM; }
+    m->cfg = *cfg;
+    m->err[0] = 0;
+    err = m->err;
+    int S = cfg->input_size;
+    m->sp[0] = S;
+    m->sp[1] = conv_valid(S, 3, 2);
+    m->sp[2] = conv_valid(m->sp[1], 3, 1);
+    for (int i = 3; i < 7; ++i) m->sp[i] = same_out(m->sp[i - 1], 2);
+    m->esz = cfg->precision == KDL_PRECISION_F32 ? 4 : 2;
+    m->tma.init();
+    if (cfg->precision == KDL_PRECISION_BF16 && cfg->gemm_impl == KDL_GEMM_AUTO && !m->tma.ok()) {
+        set_err(g_err, "kdl_create: cuTensorMapEncodeTiled entry point not available");
+        delete m;
+        return KDL_ECUDA;
+    }
+    const int *sp = m->sp;
+    const size_t MB = cfg->max_batch;
+    auto sq = [](int h) { return (size_t)h * h; };
+    size_t maxel = 0;
+    size_t cands[] = {sq(sp[1]) * 32, sq(sp[2]) * 128, sq(sp[3]) * 256, sq(sp[4]) * 728, sq(sp[5]) * 1024, sq(sp[6]) * 2048};
+    for (size_t c : cands) maxel = c > maxel ? c : maxel;
+    size_t rel = 0;
+    size_t rc_[] = {sq(sp[3]) * 128, sq(sp[4]) * 256, sq(sp[5]) * 728, sq(sp[6]) * 1024};
+    for (size_t c : rc_) rel = c > rel ? c : rel;
+    size_t sel = 0;
+    size_t sc_[] = {sq(sp[3]) * 64, sq(sp[4]) * 128, sq(sp[5]) * 256, sq(sp[6]) * 728};
+    for (size_t c : sc_) sel = c > sel ? c : sel;
+    int rc = KDL_OK;
+    // +tile slack: TMA boxes of the last M tile may read past M rows (results are discarded)
+    size_t slack = 256 * 2048;
+    if ((rc = dev_alloc(m, &m->X, (MB * maxel + slack) * m->esz)) || (rc = dev_alloc(m, &m->T, (MB * maxel + slack) * m->esz)) ||
+        (rc = dev_alloc(m, &m->U, (MB * maxel + slack) * m->esz)) || (rc = dev_alloc(m, &m->R, (MB * rel + slack) * m->esz)) ||
+        (rc = dev_alloc(m, &m->S, (MB * sel + slack) * m->esz)) ||
+        (rc = dev_alloc(m, (void **)&m->u8img, MB * sq(S) * 3 + 16)) ||
+        (rc = dev_alloc(m, (void **)&m->d_logits, MB * 10 * 4)) ||
+        (rc = dev_alloc(m, (void **)&m->d_meta, MB * sizeof(ImgMeta) * KdlModel::NSLOT)) ||
+        (rc = dev_alloc(m, (void **)&m->d_xtab, MB * S * 4)) || (rc = dev_alloc(m, (void **)&m->d_ytab, MB * S * 4))) {
+        set_err(g_err, "%s", m->err);
+        kdl_destroy(m);
+        return rc;
+    }
+    for (int i = 0; i < KdlModel::NSLOT; ++i) {
+        CK(cudaMallocHost((void **)&m->h_meta[i], MB * sizeof(ImgMeta)));
+        CK(cudaEventCreateWithFlags(&m->slot_ev[i], cudaEventDisableTiming));
+    }
+    CK(cudaStreamCreateWithFlags(&m->own_stream, cudaStreamNonBlocking));
+    CK(cudaFuncSetAttribute(k_gap_head<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
+    CK(cudaFuncSetAttribute(k_gap_head<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
+    if ((rc = tc::configure(m->err)) != KDL_OK) { set_err(g_err, "%s", m->err); kdl_destroy(m); return rc; }
+    *out = m;
+    return KDL_OK;
+}
+
+extern "C" int kdl_destroy(KdlModel *m) {
+    if (!m) return KDL_OK;
+    cudaSetDevice(m->cfg.device);
+    cudaDeviceSynchronize();
+    for (void *p : m->owned) cudaFree(p);
+    if (m->d_src) cudaFree(m->d_src);
+    if (m->d_in_f32) cudaFree(m->d_in_f32);
+    for (int i = 0; i < KdlModel::NSLOT; ++i) {
+        if (m->h_meta[i]) { cudaFreeHost(m->h_meta[i]); cudaEventDestroy(m->slot_ev[i]); }
+    }
+    if (m->own_stream) cudaStreamDestroy(m->own_stream);
+    delete m;
+    return KDL_OK;
+}
+
+extern "C" const char *kdl_last_error(const KdlModel *m) { return m ? m->err : g_err; }
+extern "C" int kdl_last_launch_count(const KdlModel *m) { return m ? m->launches : 0; }
+extern "C" const char *kdl_version(void) {
+    return "kdl 0.1 sm_100a: k_resize k_conv1 k_dw3x3 k_maxpool_add k_gap_head k_gemm_simple k_gemm_tc(tcgen05/TMEM/TMA)";
+}
+
+// ---------------------------------------------------------------------------------------------------
+// calls
+// ---------------------------------------------------------------------------------------------------
+static int check_call(KdlModel *m, int B, bool need_weights) {
+    if (!m) { set_err(g_err, "null model"); return KDL_EINVAL; }
+    if (B < 1 || B > m->cfg.max_batch) {
+        set_err(m->err, "batch %d outside [1, max_batch=%d]", B, m->cfg.max_batch);
+        return KDL_EINVAL;
+    }
+    if (need_weights && !m->weights_loaded) { set_err(m->err, "kdl_load_weights has not been called"); return KDL_ESTATE; }
+    cudaError_t e = cudaSetDevice(m->cfg.device);
+    if (e != cudaSuccess) { set_err(m->err, "cudaSetDevice: %s", cudaGetErrorString(e)); return KDL_ECUDA; }
+    return KDL_OK;
+}
+
+// uploads per-image metadata and builds the index tables
+static int stage_meta(KdlModel *m, const int64_t *offset, const int32_t *h, const int32_t *w, const int64_t *pitch,
+                      int B, cudaStream_t st, ImgMeta **d_meta_out) {
+    char *err = m->err;
+    if (!offset || !h || !w || !pitch) { set_err(err, "null metadata array"); return KDL_EINVAL; }
+    for (int i = 0; i < B; ++i) {
+        if (h[i] < 1 || w[i] < 1 || pitch[i] < (int64_t)w[i] * 3 || offset[i] < 0) {
+            set_err(err, "image %d: bad geometry h=%d w=%d pitch=%lld offset=%lld", i, h[i], w[i], (long long)pitch[i],
+                    (long long)offset[i]);
+            return KDL_EINVAL;
+        }
+    }
+    int s = m->slot;
+    m->slot = (m->slot + 1) % KdlModel::NSLOT;
+    CK(cudaEventSynchronize(m->slot_ev[s]));  // previous user of this staging slot has been copied
+    for (int i = 0; i < B; ++i) m->h_meta[s][i] = ImgMeta{offset[i], pitch[i], h[i], w[i]};
+    ImgMeta *dm = m->d_meta + (size_t)s * m->cfg.max_batch;
+    CK(cudaMemcpyAsync(dm, m->h_meta[s], B * sizeof(ImgMeta), cudaMemcpyHostToDevice, st));
+    CK(cudaEventRecord(m->slot_ev[s], st));
+    k_index_tables<<<(2 * B + 63) / 64, 64, 0, st>>>(dm, B, m->cfg.input_size, m->d_xtab, m->d_ytab);
+    LAUNCH_CHECK();
+    *d_meta_out = dm;
+    return KDL_OK;
+}
+
+extern "C" int kdl_preprocess_u8(KdlModel *m, const uint8_t *d_src, const int64_t *offset, const int32_t *h,
+                                 const int32_t *w, const int64_t *pitch, int32_t B, float *d_out, void *stream) {
+    int rc = check_call(m, B, false);
+    if (rc) return rc;
+    if (!d_src || !d_out) { set_err(m->err, "kdl_preprocess_u8: null buffer"); return KDL_EINVAL; }
+    cudaStream_t st = (cudaStream_t)stream;
+    m->launches = 0;
+    ImgMeta *dm;
+    if ((rc = stage_meta(m, offset, h, w, pitch, B, st, &dm))) return rc;
+    int S = m->cfg.input_size;
+    long long total = (long long)B * S * S * 3;
+    k_resize<float><<<(unsigned)((total / 4 + 256) / 256), 256, 0, st>>>(d_src, dm, m->d_xtab, m->d_ytab, B, S, d_out);
+    LAUNCH_CHECK();
+    return KDL_OK;
+}
+
+static int run_forward(KdlModel *m, const float *in_f32, const uint8_t *in_u8, int B, float *d_logits, cudaStream_t st) {
+    m->last_B = B;
+    if (m->cfg.precision == KDL_PRECISION_F32) {
+        Runner<float> r{m, st, B};
+        return r.forward(in_f32, in_u8, d_logits);
+    }
+    Runner<bf16> r{m, st, B};
+    return r.forward(in_f32, in_u8, d_logits);
+}
+
+extern "C" int kdl_forward(KdlModel *m, const float *d_input_8, int32_t B, float *d_dense_7, void *stream) {
+    int rc = check_call(m, B, true);
+    if (rc) return rc;
+    if (!d_input_8 || !d_dense_7) { set_err(m->err, "kdl_forward: null buffer"); return KDL_EINVAL; }
+    m->launches = 0;
+    return run_forward(m, d_input_8, nullptr, B, d_dense_7, (cudaStream_t)stream);
+}
+
+extern "C" int kdl_predict_u8(KdlModel *m, const uint8_t *d_src, const int64_t *offset, const int32_t *h,
+                              const int32_t *w, const int64_t *pitch, int32_t B, float *d_dense_7, void *stream) {
+    int rc = check_call(m, B, true);
+    if (rc) return rc;
+    if (!d_src || !d_dense_7) { set_err(m->err, "kdl_predict_u8: null buffer"); return KDL_EINVAL; }
+    cudaStream_t st = (cudaStream_t)stream;
+    m->launches = 0;
+    ImgMeta *dm;
+    if ((rc = stage_meta(m, offset, h, w, pitch, B, st, &dm))) return rc;
+    int S = m->cfg.input_size;
+    long long total = (long long)B * S * S * 3;
+    // resized uint8 stays 1 byte/px; the x/127.5-1 scaling is applied (bit-exactly) inside block1_conv1's load
+    k_resize<uint8_t><<<(unsigned)((total / 4 + 256) / 256), 256, 0, st>>>(d_src, dm, m->d_xtab, m->d_ytab, B, S, m->u8img);
+    LAUNCH_CHECK();
+    return run_forward(m, nullptr, m->u8img, B, d_dense_7, st);
+}
+
+extern "C" int kdl_predict_u8_host(KdlModel *m, const uint8_t *h_src, size_t total_bytes, const int64_t *offset,
+                                   const int32_t *h, const int32_t *w, const int64_t *pitch, int32_t B,
+                                   float *h_dense_7) {
+    int rc = check_call(m, B, true);
+    if (rc) return rc;
+    char *err = m->err;
+    if (!h_src || !h_dense_7 || total_bytes == 0) { set_err(err, "kdl_predict_u8_host: null buffer"); return KDL_EINVAL; }
+    for (int i = 0; i < B; ++i) {
+        if (offset && pitch && h && (size_t)(offset[i] + (int64_t)(h[i] - 1) * pitch[i] + (int64_t)w[i] * 3) > total_bytes) {
+            set_err(err, "image %d extends past total_bytes", i);
+            return KDL_EINVAL;
+        }
+    }
+    if (total_bytes > m->d_src_cap) {
+        if (m->d_src) CK(cudaFree(m->d_src));
+        m->d_src = nullptr; m->d_src_cap = 0;
+        size_t cap = total_bytes + total_bytes / 4;
+        CK(cudaMalloc((void **)&m->d_src, cap));
+        m->d_src_cap = cap;
+    }
+    cudaStream_t st = m->own_stream;
+    CK(cudaMemcpyAsync(m->d_src, h_src, total_bytes, cudaMemcpyHostToDevice, st));
+    rc = kdl_predict_u8(m, m->d_src, offset, h, w, pitch, B, m->d_logits, st);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(h_dense_7, m->d_logits, (size_t)B * 10 * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return KDL_OK;
+}
+
+extern "C" int kdl_forward_host(KdlModel *m, const float *h_input_8, int32_t B, float *h_dense_7) {
+    int rc = check_call(m, B, true);
+    if (rc) return rc;
+    char *err = m->err;
+    if (!h_input_8 || !h_dense_7) { set_err(err, "kdl_forward_host: null buffer"); return KDL_EINVAL; }
+    size_t S = m->cfg.input_size;
+    if (!m->d_in_f32) CK(cudaMalloc((void **)&m->d_in_f32, (size_t)m->cfg.max_batch * S * S * 3 * 4));
+    cudaStream_t st = m->own_stream;
+    CK(cudaMemcpyAsync(m->d_in_f32, h_input_8, (size_t)B * S * S * 3 * 4, cudaMemcpyHostToDevice, st));
+    rc = kdl_forward(m, m->d_in_f32, B, m->d_logits, st);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(h_dense_7, m->d_logits, (size_t)B * 10 * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return KDL_OK;
+}
+
+extern "C" int kdl_num_taps(const KdlModel *m) { return m ? (int)m->taps.size() : 0; }
+extern "C" const char *kdl_tap_name(const KdlModel *m, int32_t i) {
+    if (!m || i < 0 || i >= (int)m->taps.size()) return nullptr;
+    return m->taps[i].name.c_str();
+}
+
+extern "C" int kdl_layer_output(KdlModel *m, const char *tapname, float *d_out, size_t capacity, int32_t shape4[4],
+                                int32_t *relu_applied, void *stream) {
+    if (!m || !tapname) { set_err(g_err, "kdl_layer_output: null argument"); return KDL_EINVAL; }
+    char *err = m->err;
+    if (!m->cfg.keep_taps) { set_err(err, "kdl_layer_output: model was created with keep_taps=0"); return KDL_ESTATE; }
+    int i = find_tap(m, tapname);
+    if (i < 0) { set_err(err, "kdl_layer_output: unknown tap '%s' (run a forward first)", tapname); return KDL_EINVAL; }
+    const Tap &t = m->taps[i];
+    size_t n = (size_t)m->last_B * t.H * t.H * t.C;
+    if (shape4) { shape4[0] = m->last_B; shape4[1] = t.H; shape4[2] = t.H; shape4[3] = t.C; }
+    if (relu_applied) *relu_applied = t.relu_applied;
+    if (!d_out) return KDL_OK;
+    if (capacity < n) { set_err(err, "kdl_layer_output: capacity %zu < %zu", capacity, n); return KDL_EINVAL; }
+    CK(cudaSetDevice(m->cfg.device));
+    cudaStream_t st = (cudaStream_t)stream;
+    if (t.is_float) {
+        CK(cudaMemcpyAsync(d_out, t.buf, n * 4, cudaMemcpyDeviceToDevice, st));
+    } else if (m->cfg.precision == KDL_PRECISION_F32) {
+        k_to_f32<float><<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const float *)t.buf, d_out, n);
+    } else {
+        k_to_f32<bf16><<<(unsigned)((n + 255) / 256), 256, 0, st>>>((const bf16 *)t.buf, d_out, n);
+    }
+    CK(cudaGetLastError());
+    return KDL_OK;
+}
+
+extern "C" int kdl_gemm_bf16(const void *d_A, const void *d_Wt, const float *d_bias, const void *d_residual, void *d_out,
+                             int32_t M, int32_t N, int32_t K, int32_t relu, void *stream) {
+    static thread_local tc::TmaEncoder enc;
+    char *err = g_err;
+    if (!d_A || !d_Wt || !d_bias || !d_out || M < 1) { set_err(g_err, "kdl_gemm_bf16: null argument"); return KDL_EINVAL; }
+    if (!tc::shape_supported(M, N, K)) { set_err(g_err, "kdl_gemm_bf16: unsupported shape M=%d N=%d K=%d (N,K must be multiples of 8)", M, N, K); return KDL_EINVAL; }
+    if (!enc.ok()) enc.init();
+    if (!enc.ok()) { set_err(g_err, "kdl_gemm_bf16: cuTensorMapEncodeTiled unavailable"); return KDL_ECUDA; }
+    int rc = tc::configure(g_err);
+    if (rc) return rc;
+    CUtensorMap tmB;
+    if (!enc.encode_2d(&tmB, d_Wt, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, tc::BLOCK_K, tc::BLOCK_N)) {
+        set_err(g_err, "kdl_gemm_bf16: tensor map encode failed");
+        return KDL_ECUDA;
+    }
+    (void)err;
+    return tc::launch_gemm(enc, (const bf16 *)d_A, (const bf16 *)d_Wt, &tmB, d_bias, (const bf16 *)d_residual, (bf16 *)d_out, M, N, K,
+                           relu, (cudaStream_t)stream, g_err);
+}

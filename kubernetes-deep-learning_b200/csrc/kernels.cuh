@@ -1,0 +1,417 @@
+// CUDA-core kernels of the Xception path (sm_100a): preprocessing, entry conv, depthwise, pooling, head,
+// and the CUDA-core GEMM used by the fp32 path / as the kernel-vs-kernel reference of the tcgen05 GEMM.
+// Storage type T in {float, bf16}; arithmetic is fp32.  Layout everywhere: NHWC, channels innermost.
+#pragma once
+#include "common.cuh"
+
+namespace kdl {
+
+// ---------------------------------------------------------------------------------------------------
+// K1: gateway preprocessing (model_server.py:18,53 -> Pillow NEAREST resize + x/127.5-1)
+// ---------------------------------------------------------------------------------------------------
+struct ImgMeta {
+    int64_t offset;  // byte offset of pixel (0,0) from the batch base pointer
+    int64_t pitch;   // bytes per source row
+    int32_t h, w;
+};
+
+// One thread per (image, axis): Pillow's serial accumulated-double rule, reproduced operation for operation
+// (a = n_in/n_out; o = a*0.5; idx = (int)o; o += a).  A closed form is NOT bit-exact.
+__global__ void k_index_tables(const ImgMeta *__restrict__ meta, int B, int S, int32_t *__restrict__ xtab,
+                               int32_t *__restrict__ ytab) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= 2 * B) return;
+    int b = t >> 1, axis = t & 1;
+    int n_in = axis ? meta[b].h : meta[b].w;
+    int32_t *tab = (axis ? ytab : xtab) + (size_t)b * S;
+    double a = __ddiv_rn((double)n_in, (double)S);
+    double o = __dmul_rn(a, 0.5);
+    for (int i = 0; i < S; ++i) {
+        int s = o < 0.0 ? -1 : (int)o;  // Pillow COORD()
+        s = max(0, min(s, n_in - 1));
+        tab[i] = s;
+        o = __dadd_rn(o, a);  // accumulated, never i*a, never fused
+    }
+}
+
+// Gather + (optional) scale.  Flat over the B*S*S*3 output elements, 4 consecutive elements per thread so the
+// store is one aligned 16-byte (float) or 4-byte (uint8) vector and a warp writes 512 / 128 contiguous bytes.
+template <typename TOut> struct PxOut;
+template <> struct PxOut<float> {
+    static __device__ __forceinline__ float cvt(uint8_t v) { return scale_px(v); }
+    static __device__ __forceinline__ void st4(float *p, float a, float b, float c, float d) {
+        *reinterpret_cast<float4 *>(p) = make_float4(a, b, c, d);
+    }
+};
+template <> struct PxOut<uint8_t> {
+    static __device__ __forceinline__ uint8_t cvt(uint8_t v) { return v; }
+    static __device__ __forceinline__ void st4(uint8_t *p, uint8_t a, uint8_t b, uint8_t c, uint8_t d) {
+        *reinterpret_cast<uchar4 *>(p) = make_uchar4(a, b, c, d);
+    }
+};
+
+template <typename TOut>
+__global__ void k_resize(const uint8_t *__restrict__ src, const ImgMeta *__restrict__ meta,
+                         const int32_t *__restrict__ xtab, const int32_t *__restrict__ ytab, int B, int S,
+                         TOut *__restrict__ out) {
+    const long long per_img = (long long)S * S * 3;
+    const long long total = per_img * B;
+    long long g = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (g >= total) return;
+    const int row_el = S * 3;
+    int b = (int)(g / per_img);
+    int r = (int)(g - (long long)b * per_img);
+    int y = r / row_el;
+    int j = r - y * row_el;
+    int x = j / 3, c = j - x * 3;
+    TOut v[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        if (g + e < total) {
+            const ImgMeta mt = meta[b];
+            const uint8_t *p = src + mt.offset + (long long)ytab[(size_t)b * S + y] * mt.pitch +
+                               (long long)xtab[(size_t)b * S + x] * 3 + c;
+            v[e] = PxOut<TOut>::cvt(__ldg(p));
+        } else {
+            v[e] = TOut(0);
+        }
+        if (++c == 3) { c = 0; if (++x == S) { x = 0; if (++y == S) { y = 0; ++b; } } }
+    }
+    if (g + 4 <= total) {
+        PxOut<TOut>::st4(out + g, v[0], v[1], v[2], v[3]);
+    } else {
+        for (int e = 0; g + e < total; ++e) out[g + e] = v[e];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// K2: block1_conv1  3x3 s2 VALID, 3 -> 32, folded BN + ReLU.  Input is the serving_default float tensor or
+// the resized uint8 image (scaled on load with the gateway's exact arithmetic).  Memory-bound, K=27.
+// One thread = one output pixel x 8 output channels (4 threads per pixel -> 64 B contiguous per pixel).
+// ---------------------------------------------------------------------------------------------------
+template <typename TIn> __device__ __forceinline__ float in_px(const TIn *p);
+template <> __device__ __forceinline__ float in_px<float>(const float *p) { return __ldg(p); }
+template <> __device__ __forceinline__ float in_px<uint8_t>(const uint8_t *p) { return scale_px(__ldg(p)); }
+
+template <typename TIn, typename T>
+__global__ void __launch_bounds__(256)
+k_conv1(const TIn *__restrict__ in, const float *__restrict__ w /*[27][32]*/, const float *__restrict__ bias,
+        T *__restrict__ out, int B, int S, int Ho) {
+    __shared__ float ws[27 * 32];
+    __shared__ float bs[32];
+    for (int i = threadIdx.x; i < 27 * 32; i += blockDim.x) ws[i] = w[i];
+    if (threadIdx.x < 32) bs[threadIdx.x] = bias[threadIdx.x];
+    __syncthreads();
+    long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    long long npix = (long long)B * Ho * Ho;
+    long long pix = t >> 2;
+    int cg = (int)(t & 3);
+    if (pix >= npix) return;
+    int b = (int)(pix / (Ho * Ho));
+    int r = (int)(pix - (long long)b * Ho * Ho);
+    int oy = r / Ho, ox = r - oy * Ho;
+    const TIn *base = in + (((long long)b * S + 2 * oy) * S + 2 * ox) * 3;
+    float acc[8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) acc[c] = 0.f;
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky) {
+#pragma unroll
+        for (int kk = 0; kk < 9; ++kk) {  // kx*3+ci : 9 contiguous input values per kernel row
+            float v = in_px<TIn>(base + (long long)ky * S * 3 + kk);
+            const float4 *wp = reinterpret_cast<const float4 *>(&ws[(ky * 9 + kk) * 32 + cg * 8]);
+            float4 w0 = wp[0], w1 = wp[1];
+            acc[0] = fmaf(v, w0.x, acc[0]); acc[1] = fmaf(v, w0.y, acc[1]);
+            acc[2] = fmaf(v, w0.z, acc[2]); acc[3] = fmaf(v, w0.w, acc[3]);
+            acc[4] = fmaf(v, w1.x, acc[4]); acc[5] = fmaf(v, w1.y, acc[5]);
+            acc[6] = fmaf(v, w1.z, acc[6]); acc[7] = fmaf(v, w1.w, acc[7]);
+        }
+    }
+    T *o = out + pix * 32 + cg * 8;
+    float4 a0 = make_float4(acc[0] + bs[cg * 8 + 0], acc[1] + bs[cg * 8 + 1], acc[2] + bs[cg * 8 + 2], acc[3] + bs[cg * 8 + 3]);
+    float4 a1 = make_float4(acc[4] + bs[cg * 8 + 4], acc[5] + bs[cg * 8 + 5], acc[6] + bs[cg * 8 + 6], acc[7] + bs[cg * 8 + 7]);
+    V4<T>::st(o, relu4(a0));
+    V4<T>::st(o + 4, relu4(a1));
+}
+
+// ---------------------------------------------------------------------------------------------------
+// K4: depthwise 3x3 s1 SAME (zero pad 1), optional ReLU on load.  Memory-bound.
+// In NHWC one image row is a contiguous run of W*C values, so the op is a 3-row stencil with taps at
+// -C, 0, +C along the flattened row: every load and store is fully coalesced.  Each thread owns 4 channels
+// of one column and slides down `rows` output rows with the 3x3 window and its 9x4 weights in registers.
+// ---------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(128)
+k_dw3x3(const T *__restrict__ in, const float *__restrict__ w /*[9][C]*/, T *__restrict__ out, int H, int W,
+        int C, int relu_in, int rows) {
+    const int CV = C >> 2;
+    const int v = blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= W * CV) return;
+    const int x = v / CV;
+    const int c = (v - x * CV) << 2;
+    const int y0 = blockIdx.y * rows;
+    const int b = blockIdx.z;
+    float4 wk[9];
+#pragma unroll
+    for (int t = 0; t < 9; ++t) wk[t] = __ldg(reinterpret_cast<const float4 *>(w + (size_t)t * C + c));
+    const T *base = in + (size_t)b * H * W * C + (size_t)x * C + c;
+    T *obase = out + (size_t)b * H * W * C + (size_t)x * C + c;
+    const bool hasL = x > 0, hasR = x < W - 1;
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    float4 r0[3], r1[3], r2[3];
+    auto loadrow = [&](int yy, float4 *r) {
+        if (yy < 0 || yy >= H) {
+            r[0] = z; r[1] = z; r[2] = z;
+        } else {
+            const T *p = base + (size_t)yy * W * C;
+            r[1] = V4<T>::ld(p);
+            r[0] = hasL ? V4<T>::ld(p - C) : z;
+            r[2] = hasR ? V4<T>::ld(p + C) : z;
+            if (relu_in) { r[0] = relu4(r[0]); r[1] = relu4(r[1]); r[2] = relu4(r[2]); }
+        }
+    };
+    loadrow(y0 - 1, r0);
+    loadrow(y0, r1);
+    const int y1 = min(y0 + rows, H);
+    for (int y = y0; y < y1; ++y) {
+        loadrow(y + 1, r2);
+        float4 acc = z;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            acc = fma4(r0[k], wk[k], acc);
+            acc = fma4(r1[k], wk[3 + k], acc);
+            acc = fma4(r2[k], wk[6 + k], acc);
+        }
+        V4<T>::st(obase + (size_t)y * W * C, acc);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) { r0[k] = r1[k]; r1[k] = r2[k]; }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// K6: MaxPooling2D(3, strides 2, 'same') with TF padding (pad_lo = 0 for even inputs, 1 for odd; -inf pad)
+// fused with the residual add.  One thread = one output pixel x 4 channels.
+// ---------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_maxpool_add(const T *__restrict__ in, const T *__restrict__ res, T *__restrict__ out, int B, int H, int W,
+              int C, int Ho, int Wo, int pad_lo) {
+    const int CV = C >> 2;
+    long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    long long total = (long long)B * Ho * Wo * CV;
+    if (t >= total) return;
+    int cv = (int)(t % CV);
+    long long p = t / CV;
+    int ox = (int)(p % Wo);
+    long long q = p / Wo;
+    int oy = (int)(q % Ho);
+    int b = (int)(q / Ho);
+    const int c = cv << 2;
+    float4 m = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+#pragma unroll
+    for (int dy = 0; dy < 3; ++dy) {
+        int iy = 2 * oy - pad_lo + dy;
+        if (iy < 0 || iy >= H) continue;
+#pragma unroll
+        for (int dx = 0; dx < 3; ++dx) {
+            int ix = 2 * ox - pad_lo + dx;
+            if (ix < 0 || ix >= W) continue;
+            m = max4(m, V4<T>::ld(in + (((size_t)b * H + iy) * W + ix) * C + c));
+        }
+    }
+    size_t o = (((size_t)b * Ho + oy) * Wo + ox) * C + c;
+    V4<T>::st(out + o, add4(m, V4<T>::ld(res + o)));
+}
+
+// Compact copy of the even-index pixels: the input of a Conv2D(1x1, strides 2, 'same') residual projection
+// seen as a dense [B*Ho*Wo, C] matrix (so the projection is a plain GEMM for the tcgen05 kernel).
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_subsample2(const T *__restrict__ in, T *__restrict__ out, int B, int H, int W, int C, int Ho, int Wo) {
+    const int CV = C >> 2;
+    long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    long long total = (long long)B * Ho * Wo * CV;
+    if (t >= total) return;
+    int cv = (int)(t % CV);
+    long long p = t / CV;
+    int ox = (int)(p % Wo);
+    long long q = p / Wo;
+    int oy = (int)(q % Ho);
+    int b = (int)(q / Ho);
+    V4<T>::st(out + p * C + cv * 4, V4<T>::ld(in + (((size_t)b * H + 2 * oy) * W + 2 * ox) * C + cv * 4));
+}
+
+// ---------------------------------------------------------------------------------------------------
+// CUDA-core GEMM with fused epilogue:  out[m,n] = act(sum_k A(m,k) W[k,n] + bias[n]) (+ res[m,n]).
+// A is addressed through a row map so the same kernel serves
+//   mode 0: dense [M,K] rows (pointwise 1x1 on a depthwise output),
+//   mode 1: Conv2D(1x1, strides 2, 'same') -- row m = pixel (b, 2oy, 2ox) of an NHWC tensor,
+//   mode 2: Conv2D(3x3, s1, VALID) with Cin = 32 as an implicit GEMM, K = 9*32 ordered (ky,kx,ci).
+// fp32 path (precision contract <= 1e-4) and kernel-vs-kernel reference for the tcgen05 GEMM.
+// ---------------------------------------------------------------------------------------------------
+struct RowMap {
+    int mode;
+    int Hin, Win, Ho, Wo, C;  // modes 1, 2
+};
+
+__device__ __forceinline__ long long row_offset(const RowMap &rm, int m, int K) {
+    if (rm.mode == 0) return (long long)m * K;
+    int hw = rm.Ho * rm.Wo;
+    int b = m / hw;
+    int r = m - b * hw;
+    int oy = r / rm.Wo, ox = r - oy * rm.Wo;
+    int s = rm.mode == 1 ? 2 : 1;
+    return (((long long)b * rm.Hin + s * oy) * rm.Win + s * ox) * rm.C;
+}
+
+constexpr int GS_BM = 128, GS_BN = 64, GS_BK = 16;
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_gemm_simple(const T *__restrict__ A, const T *__restrict__ Wkn, const float *__restrict__ bias,
+              const T *res, T *out, int M, int N, int K, int relu, RowMap rm) {
+    __shared__ __align__(16) float As[GS_BK][GS_BM + 4];
+    __shared__ __align__(16) float Bs[GS_BK][GS_BN];
+    const int tid = threadIdx.x;
+    const int m0 = blockIdx.y * GS_BM, n0 = blockIdx.x * GS_BN;
+    // A loader: thread -> (row = tid/2, 8 consecutive k)
+    const int arow = tid >> 1, akoff = (tid & 1) * 8;
+    const int am = m0 + arow;
+    const long long aoff = am < M ? row_offset(rm, am, K) : 0;
+    // B loader: thread -> (k = tid/16, 4 consecutive n)
+    const int bk = tid >> 4, bn = (tid & 15) * 4;
+    const int ty = tid >> 4, tx = tid & 15;  // 16 x 16 thread grid: 8 rows x 4 cols each
+    float acc[8][4];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+    for (int k0 = 0; k0 < K; k0 += GS_BK) {
+        // implicit-GEMM tap offset (mode 2): k-block lies inside one (ky,kx) tap because 32 % 16 == 0
+        long long koff = k0;
+        if (rm.mode == 2) {
+            int tap = k0 / rm.C, ci = k0 - tap * rm.C;
+            int ky = tap / 3, kx = tap - ky * 3;
+            koff = ((long long)ky * rm.Win + kx) * rm.C + ci;
+        }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            int k = k0 + akoff + h * 4;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (am < M && k + 4 <= K) v = V4<T>::ld(A + aoff + koff + akoff + h * 4);
+            As[akoff + h * 4 + 0][arow] = v.x;
+            As[akoff + h * 4 + 1][arow] = v.y;
+            As[akoff + h * 4 + 2][arow] = v.z;
+            As[akoff + h * 4 + 3][arow] = v.w;
+        }
+        {
+            int k = k0 + bk, n = n0 + bn;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (k < K && n + 4 <= N) v = V4<T>::ld(Wkn + (long long)k * N + n);
+            *reinterpret_cast<float4 *>(&Bs[bk][bn]) = v;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < GS_BK; ++k) {
+            float4 a0 = *reinterpret_cast<const float4 *>(&As[k][ty * 8]);
+            float4 a1 = *reinterpret_cast<const float4 *>(&As[k][ty * 8 + 4]);
+            float4 bv = *reinterpret_cast<const float4 *>(&Bs[k][tx * 4]);
+            float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+            float bb[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], bb[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+    const int n = n0 + tx * 4;
+    if (n + 4 > N) return;
+    float4 bv = *reinterpret_cast<const float4 *>(bias + n);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        int m = m0 + ty * 8 + i;
+        if (m >= M) break;
+        float4 v = make_float4(acc[i][0] + bv.x, acc[i][1] + bv.y, acc[i][2] + bv.z, acc[i][3] + bv.w);
+        if (relu) v = relu4(v);
+        size_t o = (size_t)m * N + n;
+        if (res) v = add4(v, V4<T>::ld(res + o));
+        V4<T>::st(out + o, v);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// K7 + head: GlobalAveragePooling2D -> [Dense(N1)+bias, ReLU] -> Dense(N2)+bias.  One CTA per image.
+// (N1 == 0 means the head is a single Dense(C -> N2).)  Warp-level reductions; 0.002 % of the MACs.
+// ---------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+k_gap_head(const T *__restrict__ in, int HW, int C, const float *__restrict__ W1, const float *__restrict__ b1,
+           int N1, const float *__restrict__ W2, const float *__restrict__ b2, int N2,
+           float *__restrict__ feat_out /*nullable [B,C]*/, float *__restrict__ logits) {
+    extern __shared__ float sm[];
+    float *feat = sm;            // [C]
+    float *part = sm + C;        // [8][128]
+    float *hid = part + 8 * 128; // [128]
+    const int b = blockIdx.x, tid = threadIdx.x;
+    const T *base = in + (size_t)b * HW * C;
+    const float inv = 1.0f / (float)HW;
+    for (int c = tid * 4; c < C; c += blockDim.x * 4) {
+        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int p = 0; p < HW; ++p) s = add4(s, V4<T>::ld(base + (size_t)p * C + c));
+        feat[c] = s.x * inv; feat[c + 1] = s.y * inv; feat[c + 2] = s.z * inv; feat[c + 3] = s.w * inv;
+    }
+    __syncthreads();
+    if (feat_out)
+        for (int c = tid; c < C; c += blockDim.x) feat_out[(size_t)b * C + c] = feat[c];
+    const int warp = tid >> 5, lane = tid & 31;
+    const int Nd = N1 > 0 ? N1 : N2;             // width of the first dense
+    const float *Wd = N1 > 0 ? W1 : W2;
+    // first dense: warp w takes k in its slice, lane handles outputs lane, lane+32, lane+64, lane+96
+    {
+        float a[4] = {0.f, 0.f, 0.f, 0.f};
+        int kper = (C + 7) / 8;
+        int k0 = warp * kper, k1 = min(C, k0 + kper);
+        for (int k = k0; k < k1; ++k) {
+            float f = feat[k];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                int n = lane + 32 * j;
+                if (n < Nd) a[j] = fmaf(f, __ldg(Wd + (size_t)k * Nd + n), a[j]);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) part[warp * 128 + lane + 32 * j] = a[j];
+    }
+    __syncthreads();
+    if (tid < Nd) {
+        float s = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) s += part[w * 128 + tid];
+        if (N1 > 0) {
+            hid[tid] = fmaxf(s + b1[tid], 0.f);
+        } else {
+            logits[(size_t)b * N2 + tid] = s + b2[tid];
+        }
+    }
+    if (N1 == 0) return;
+    __syncthreads();
+    // second dense: one warp per output, shuffle reduction
+    for (int n = warp; n < N2; n += 8) {
+        float s = 0.f;
+        for (int k = lane; k < N1; k += 32) s = fmaf(hid[k], __ldg(W2 + (size_t)k * N2 + n), s);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) logits[(size_t)b * N2 + n] = s + b2[n];
+    }
+}
+
+// storage -> float32 copy (debug taps)
+template <typename T>
+__global__ void k_to_f32(const T *__restrict__ in, float *__restrict__ out, size_t n) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = ld1<T>(in + i);
+}
+
+}  // namespace kdl

@@ -1,0 +1,126 @@
+"""GPU parity of the Xception forward (through the C ABI) against the fp64 oracle.
+
+Tolerances (BASELINE.json north_star): rel = max|a-b| / max|b| per image;
+  fp32 path <= 1e-4;   bf16 path <= 2e-2 with identical top-1.  Layer-wise on the calibrated init, because
+  a logits-only check is blind to the middle flow under Keras-default init."""
+import numpy as np
+import pytest
+import torch
+
+from gpu_util import rel, synth_inputs
+
+pytestmark = pytest.mark.gpu
+
+F32_TOL = 1e-4
+BF16_TOL = 2e-2
+
+
+def _oracle(W, x, taps=None):
+    from oracle import xception_oracle as xo
+    return xo.forward(W, x, torch.float64, taps)
+
+
+def _mk(W, **kw):
+    import kdl_b200  # noqa: F401
+    from kdl_b200 import engine
+    return engine.Model(W, **kw)
+
+
+@pytest.mark.parametrize("h", [299, 150])
+@pytest.mark.parametrize("init", ["calibrated", "keras_default"])
+def test_fp32_path_logits_and_layers(h, init):
+    from kdl_b200 import weights
+    W = weights.make_weights(1, init)
+    _, x = synth_inputs(h, 3)
+    taps = {}
+    want = _oracle(W, x, taps)
+    m = _mk(W, max_batch=4, input_size=h, precision="f32", keep_taps=True)
+    try:
+        got = m.serving_default(input_8=x)["dense_7"]
+        assert got.shape == (3, 10) and got.dtype == np.float32
+        for i in range(3):
+            assert rel(got[i], want[i]) <= F32_TOL, (i, got[i], want[i])
+        names = m.tap_names()
+        assert len(names) >= 50
+        for name in names:
+            a, relu = m.layer_output(name)
+            b = taps[name]
+            if relu:
+                b = np.maximum(b, 0)
+            if b.ndim == 2:
+                b = b.reshape(a.shape)
+            assert a.shape == b.shape, name
+            assert rel(a, b) <= F32_TOL, (name, rel(a, b))
+    finally:
+        m.close()
+
+
+@pytest.mark.parametrize("gemm", ["simple", "auto"])
+@pytest.mark.parametrize("h,init", [(299, "calibrated"), (150, "calibrated"), (299, "keras_default")])
+def test_bf16_path_logits_top1_and_layers(h, init, gemm):
+    from kdl_b200 import weights
+    W = weights.make_weights(1, init)
+    n = 8
+    _, x = synth_inputs(h, n)
+    taps = {}
+    want = _oracle(W, x, taps)
+    m = _mk(W, max_batch=n, input_size=h, precision="bf16", gemm_impl=gemm, keep_taps=True)
+    try:
+        got = m.serving_default(input_8=x)["dense_7"]
+        errs = [rel(got[i], want[i]) for i in range(n)]
+        assert max(errs) <= BF16_TOL, errs
+        assert (got.argmax(1) == want.argmax(1)).all()
+        worst = 0.0
+        for name in m.tap_names():
+            a, relu = m.layer_output(name)
+            b = taps[name]
+            if relu:
+                b = np.maximum(b, 0)
+            b = b.reshape(a.shape)
+            e = rel(a, b)
+            worst = max(worst, e)
+            # per-layer drift stays within the end-to-end bf16 budget (keras_default branches are ~1e-6 of the
+            # skip path, so only their block outputs are meaningful there)
+            if init == "calibrated" or name.endswith("_out") or name.startswith("block1"):
+                assert e <= BF16_TOL, (name, e)
+        print(f"bf16 {gemm} h={h} {init}: logits rel {max(errs):.2e}, worst layer rel {worst:.2e}")
+    finally:
+        m.close()
+
+
+def test_fused_uint8_path_matches_two_step():
+    """predict_uint8 (resize+scale fused into the conv1 load) == preprocess then serving_default."""
+    from kdl_b200 import weights
+    W = weights.make_weights(1, "calibrated")
+    rng = np.random.default_rng(11)
+    imgs = [rng.integers(0, 256, (int(rng.integers(64, 900)), int(rng.integers(64, 900)), 3), dtype=np.uint8)
+            for _ in range(5)]
+    for prec in ("f32", "bf16"):
+        m = _mk(W, max_batch=8, precision=prec)
+        try:
+            x = m.preprocess_uint8(imgs)
+            two = m.forward_device(x).cpu().numpy()
+            one = m.predict_uint8(imgs)
+            assert one.shape == (5, 10)
+            np.testing.assert_array_equal(one, two)   # same arithmetic, same kernels after conv1's load
+        finally:
+            m.close()
+
+
+def test_batch_split_and_head_variant():
+    from kdl_b200 import weights
+    from oracle import xception_oracle as xo
+    W = weights.make_weights(3, "calibrated", head_inner=0)
+    _, x = synth_inputs(150, 5, seed=5)
+    want = xo.forward(W, x, torch.float64)
+    m = _mk(W, max_batch=2, input_size=150, precision="f32")     # 5 images through max_batch 2 -> 3 calls
+    try:
+        got = m.serving_default(input_8=x)["dense_7"]
+        for i in range(5):
+            assert rel(got[i], want[i]) <= F32_TOL
+        with pytest.raises(KeyError):
+            m.serving_default(images=x)
+        with pytest.raises(ValueError):
+            m.serving_default(input_8=x[:, :100])
+    finally:
+        m.close()

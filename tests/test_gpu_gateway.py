@@ -1,0 +1,83 @@
+"""The drop-in contract of model_server.py on the GPU: labels, names, apply_model-shaped results."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from gpu_util import rel
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def gw():
+    import kdl_b200  # noqa: F401
+    from kdl_b200 import engine, gateway, weights
+    W = weights.make_weights(1, "calibrated")
+    m = engine.Model(W, max_batch=8, precision="bf16")
+    yield gateway.Gateway(m), W
+    m.close()
+
+
+def test_apply_model_contract_on_fixture(gw, golden_dir):
+    from kdl_b200 import gateway
+    from oracle import preprocess_oracle as po
+    from oracle import xception_oracle as xo
+    g, W = gw
+    src = np.load(os.path.join(golden_dir, "image2_fixture.npz"))["src"]
+    # the reference's call sequence (model_server.py:52-56) with the download step replaced by the fixture
+    X = g.preprocessor.from_array(src)
+    assert X.tobytes() == po.preprocess_pillow(src).tobytes()
+    req = gateway.make_request(X)
+    assert req["model_spec"] == {"name": "clothing-model", "signature_name": "serving_default"}
+    assert list(req["inputs"]) == ["input_8"]
+    res = g.Predict(req, timeout=20.0)
+    assert list(res["outputs"]) == ["dense_7"] and res["outputs"]["dense_7"].shape == (1, 10)
+    out = gateway.process_response(res)
+    assert list(out) == ['dress', 'hat', 'longsleeve', 'outwear', 'pants', 'shirt', 'shoes', 'shorts', 'skirt', 't-shirt']
+    assert all(isinstance(v, float) for v in out.values())
+    json.dumps(out)   # jsonify-able, model_server.py:66
+    want = xo.forward(W, po.preprocess_pillow(src), torch.float64)[0]
+    got = np.array(list(out.values()))
+    assert rel(got, want) <= 2e-2 and got.argmax() == want.argmax()
+    fused = g.apply_model_array(src)
+    assert list(fused) == list(out)
+    np.testing.assert_array_equal(np.array(list(fused.values()), np.float32), got.astype(np.float32))
+
+
+def test_unknown_model_or_signature_is_an_error(gw):
+    from kdl_b200 import gateway
+    g, _ = gw
+    X = np.zeros((1, 299, 299, 3), np.float32)
+    req = gateway.make_request(X)
+    req["model_spec"]["name"] = "other"
+    with pytest.raises(LookupError):
+        g.Predict(req)
+    req = gateway.make_request(X)
+    req["model_spec"]["signature_name"] = "predict"
+    with pytest.raises(LookupError):
+        g.Predict(req)
+
+
+def test_process_response_keeps_reference_batch_semantics(gw):
+    """model_server.py:47-48 zips 10 labels against the flat float list: a batch returns image 0 only."""
+    from kdl_b200 import gateway
+    r = gateway.process_response({"outputs": {"dense_7": np.arange(30, dtype=np.float32).reshape(3, 10)}})
+    assert list(r.values()) == [float(i) for i in range(10)]
+
+
+def test_predict_batch_mixed_sizes(gw):
+    from oracle import preprocess_oracle as po
+    from oracle import xception_oracle as xo
+    g, W = gw
+    rng = np.random.default_rng(2)
+    imgs = [rng.integers(0, 256, (int(rng.integers(64, 2049)), int(rng.integers(64, 2049)), 3), dtype=np.uint8)
+            for _ in range(6)]
+    res = g.predict_batch(imgs)
+    x = np.concatenate([po.preprocess_pillow(im) for im in imgs])
+    want = xo.forward(W, x, torch.float64)
+    for i, r in enumerate(res):
+        got = np.array(list(r.values()))
+        assert rel(got, want[i]) <= 2e-2 and got.argmax() == want[i].argmax()
