@@ -102,6 +102,20 @@ const char *kdl_tap_name(const KdlModel *m, int32_t i);
 int kdl_layer_output(KdlModel *m, const char *tap, float *d_out, size_t capacity, int32_t shape4[4],
                      int32_t *relu_applied, void *stream);
 
+/* Per-launch timing with CUDA events on the launching stream (bench.py's roofline numbers).  Between
+ * kdl_profile_begin and kdl_profile_end every kernel launched by this model is bracketed by two events;
+ * kdl_profile_end synchronises and returns one row per kernel class: launches, summed device ms, and the
+ * summed ALGORITHMIC flops / bytes of those launches (DESIGN.md states the per-launch formulas). */
+typedef struct KdlProfileRow {
+    char name[48];
+    int32_t launches;
+    float ms;
+    double flops;
+    double bytes;
+} KdlProfileRow;
+int kdl_profile_begin(KdlModel *m);
+int kdl_profile_end(KdlModel *m, KdlProfileRow *rows, int32_t capacity, int32_t *n_rows);
+
 /* Number of kernels the last forward/predict call launched (the bench's gpu_launches claim). */
 int kdl_last_launch_count(const KdlModel *m);
 

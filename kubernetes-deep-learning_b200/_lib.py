@@ -16,13 +16,18 @@ SYMBOLS = [
     "kdl_create", "kdl_destroy", "kdl_last_error", "kdl_weight_count", "kdl_load_weights",
     "kdl_preprocess_u8", "kdl_forward", "kdl_predict_u8", "kdl_predict_u8_host", "kdl_forward_host",
     "kdl_num_taps", "kdl_tap_name", "kdl_layer_output", "kdl_last_launch_count", "kdl_gemm_bf16",
-    "kdl_version",
+    "kdl_version", "kdl_profile_begin", "kdl_profile_end",
 ]
 
 
 class KdlConfig(ctypes.Structure):
     _fields_ = [("device", c_int32), ("max_batch", c_int32), ("input_size", c_int32), ("head_inner", c_int32),
                 ("precision", c_int32), ("gemm_impl", c_int32), ("keep_taps", c_int32), ("reserved", c_int32)]
+
+
+class KdlProfileRow(ctypes.Structure):
+    _fields_ = [("name", ctypes.c_char * 48), ("launches", c_int32), ("ms", c_float), ("flops", ctypes.c_double),
+                ("bytes", ctypes.c_double)]
 
 
 class KdlError(RuntimeError):
@@ -64,6 +69,8 @@ def load():
     lib.kdl_last_launch_count.argtypes = [P]
     lib.kdl_gemm_bf16.argtypes = [P, P, P, P, P, c_int32, c_int32, c_int32, c_int32, P]
     lib.kdl_version.restype = c_char_p
+    lib.kdl_profile_begin.argtypes = [P]
+    lib.kdl_profile_end.argtypes = [P, POINTER(KdlProfileRow), c_int32, POINTER(c_int32)]
     for s in SYMBOLS:
         fn = getattr(lib, s)
         if fn.restype is ctypes.c_int:

@@ -123,7 +123,40 @@ struct KdlModel {
     // TMA descriptors of the activation buffers viewed as [rows, K] matrices are built per call site
     std::vector<Tap> taps;
     tc::TmaEncoder tma;
+
+    // per-launch CUDA-event profiling (kdl_profile_begin / kdl_profile_end)
+    bool profiling = false;
+    struct ProfRec { int cls; cudaEvent_t a, b; };
+    std::vector<ProfRec> prof_recs;
+    std::vector<cudaEvent_t> ev_pool;
+    size_t ev_used = 0;
+    double cls_flops[16], cls_bytes[16];
+    int cls_launches[16];
 };
+
+enum ProfClass { PC_RESIZE = 0, PC_CONV1, PC_CONV2, PC_DW, PC_PW_TC_HBM, PC_PW_TC_TENSOR, PC_GEMM_SIMPLE, PC_SUBSAMPLE, PC_POOL, PC_HEAD, PC_COUNT };
+static const char *PROF_NAMES[PC_COUNT] = {"k_resize", "k_conv1", "conv2_implicit_gemm", "k_dw3x3", "k_gemm_tc[K<=256,hbm-bound]",
+                                           "k_gemm_tc[K>=728,tensor-bound]", "k_gemm_simple", "k_subsample2", "k_maxpool_add", "k_gap_head"};
+
+static cudaEvent_t prof_event(KdlModel *m) {
+    if (m->ev_used == m->ev_pool.size()) {
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        m->ev_pool.push_back(e);
+    }
+    return m->ev_pool[m->ev_used++];
+}
+static void prof_open(KdlModel *m, cudaStream_t st, int cls, double flops, double bytes) {
+    if (!m->profiling) return;
+    KdlModel::ProfRec r{cls, prof_event(m), prof_event(m)};
+    cudaEventRecord(r.a, st);
+    m->prof_recs.push_back(r);
+    m->cls_flops[cls] += flops; m->cls_bytes[cls] += bytes; m->cls_launches[cls]++;
+}
+static void prof_close(KdlModel *m, cudaStream_t st) {
+    if (!m->profiling) return;
+    cudaEventRecord(m->prof_recs.back().b, st);
+}
 
 template <typename T> struct Runner;
 
@@ -155,8 +188,7 @@ template <typename T> struct Runner {
     cudaStream_t st;
     int B;
 
-    int tap(const char *name, const void *src, int H, int C, int relu_applied, bool is_float = false) {
-        if (!m->cfg.keep_taps) return KDL_OK;
+    int alloc_tap(const char *name, int H, int C, int relu_applied, bool is_float, int *idx) {
         char *err = m->err;
         int i = find_tap(m, name);
         if (i < 0) {
@@ -168,6 +200,16 @@ template <typename T> struct Runner {
             m->taps.push_back(t);
             i = (int)m->taps.size() - 1;
         }
+        *idx = i;
+        return KDL_OK;
+    }
+
+    int tap(const char *name, const void *src, int H, int C, int relu_applied, bool is_float = false) {
+        if (!m->cfg.keep_taps) return KDL_OK;
+        char *err = m->err;
+        int i;
+        int rc = alloc_tap(name, H, C, relu_applied, is_float, &i);
+        if (rc) return rc;
         size_t bytes = (size_t)B * H * H * C * (is_float ? 4 : sizeof(T));
         CK(cudaMemcpyAsync(m->taps[i].buf, src, bytes, cudaMemcpyDeviceToDevice, st));
         return KDL_OK;
@@ -177,7 +219,9 @@ template <typename T> struct Runner {
         int rows = H >= 64 ? 8 : (H >= 16 ? 5 : H);
         int vec = H * (C / 4);
         dim3 grid((vec + 127) / 128, (H + rows - 1) / rows, B);
+        prof_open(m, st, PC_DW, 18.0 * B * H * H * C, 2.0 * B * H * H * C * sizeof(T) + 36.0 * C);
         k_dw3x3<T><<<grid, 128, 0, st>>>(in, w, out, H, H, C, relu_in, rows);
+        prof_close(m, st);
         LAUNCH_CHECK();
         return KDL_OK;
     }
@@ -188,15 +232,21 @@ template <typename T> struct Runner {
 
     // out[M,N] = act(A*W + bias) (+res).  A rows through RowMap (mode 0 = dense).
     int gemm(const T *A, const GemmW &g, const T *resid, T *out, int M, int relu, RowMap rm) {
+        const double flops = 2.0 * M * g.N * g.K;
+        const double bytes = ((double)M * g.K + (double)M * g.N * (resid ? 2 : 1) + (double)g.K * g.N) * sizeof(T) + 4.0 * g.N;
         if (use_tc() && rm.mode == 0 && tc::shape_supported(M, g.N, g.K)) {
+            prof_open(m, st, g.K >= 512 ? PC_PW_TC_TENSOR : PC_PW_TC_HBM, flops, bytes);
             int rc = tc::launch_gemm(m->tma, (const bf16 *)A, g.Wnk, &g.tmB, g.bias, (const bf16 *)resid, (bf16 *)out,
                                      M, g.N, g.K, relu, st, m->err);
+            prof_close(m, st);
             if (rc != KDL_OK) return rc;
             m->launches++;
             return KDL_OK;
         }
         dim3 grid((g.N + GS_BN - 1) / GS_BN, (M + GS_BM - 1) / GS_BM);
+        prof_open(m, st, rm.mode == 2 ? PC_CONV2 : PC_GEMM_SIMPLE, flops, bytes);
         k_gemm_simple<T><<<grid, 256, 0, st>>>(A, (const T *)g.Wkn, g.bias, resid, out, M, g.N, g.K, relu, rm);
+        prof_close(m, st);
         LAUNCH_CHECK();
         return KDL_OK;
     }
@@ -206,7 +256,9 @@ template <typename T> struct Runner {
         int M = B * Ho * Ho;
         if (use_tc() && tc::shape_supported(M, g.N, g.K)) {
             long long total = (long long)M * (g.K / 4);
+            prof_open(m, st, PC_SUBSAMPLE, 0.0, 2.0 * M * g.K * sizeof(T));
             k_subsample2<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(in, (T *)m->S, B, H, H, g.K, Ho, Ho);
+            prof_close(m, st);
             LAUNCH_CHECK();
             return gemm((const T *)m->S, g, nullptr, out, M, 0, RowMap{0, 0, 0, 0, 0, 0});
         }
@@ -218,7 +270,9 @@ template <typename T> struct Runner {
         if (pad_total < 0) pad_total = 0;
         int pad_lo = pad_total / 2;  // TF SAME: extra padding goes to the end
         long long total = (long long)B * Ho * Ho * (C / 4);
+        prof_open(m, st, PC_POOL, 0.0, ((double)B * H * H * C + 2.0 * B * Ho * Ho * C) * sizeof(T));
         k_maxpool_add<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(in, resid, out, B, H, H, C, Ho, Ho, pad_lo);
+        prof_close(m, st);
         LAUNCH_CHECK();
         return KDL_OK;
     }
@@ -239,8 +293,11 @@ template <typename T> struct Runner {
         {
             long long threads = (long long)B * sp[1] * sp[1] * 4;
             unsigned grid = (unsigned)((threads + 255) / 256);
+            prof_open(m, st, PC_CONV1, 2.0 * 27 * 32 * B * sp[1] * sp[1],
+                      (double)B * sp[0] * sp[0] * 3 * (in_f32 ? 4 : 1) + (double)B * sp[1] * sp[1] * 32 * sizeof(T));
             if (in_f32) k_conv1<float, T><<<grid, 256, 0, st>>>(in_f32, m->w_conv1, m->b_conv1, U, B, sp[0], sp[1]);
             else k_conv1<uint8_t, T><<<grid, 256, 0, st>>>(in_u8, m->w_conv1, m->b_conv1, U, B, sp[0], sp[1]);
+            prof_close(m, st);
             LAUNCH_CHECK();
             RUN(tap("block1_conv1_act", U, sp[1], 32, 1));
             // block1_conv2 as an implicit GEMM (K = 288)
@@ -313,16 +370,16 @@ template <typename T> struct Runner {
             const int H = sp[6];
             float *feat = nullptr;
             if (m->cfg.keep_taps) {
-                int i = find_tap(m, "avg_pool");
-                if (i < 0) {
-                    RUN(tap("avg_pool", m->d_logits, 1, 2048, 0, true));  // allocates; content overwritten below
-                    i = find_tap(m, "avg_pool");
-                }
+                int i;
+                RUN(alloc_tap("avg_pool", 1, 2048, 0, true, &i));
                 feat = (float *)m->taps[i].buf;
             }
             size_t smem = (2048 + 8 * 128 + 128) * sizeof(float);
+            prof_open(m, st, PC_HEAD, 2.0 * B * (2048.0 * (m->cfg.head_inner > 0 ? m->cfg.head_inner : 10)),
+                      (double)B * H * H * 2048 * sizeof(T));
             k_gap_head<T><<<B, 256, smem, st>>>(U, H * H, 2048, m->W1, m->b1, m->cfg.head_inner, m->W2, m->b2, 10,
                                                 feat, d_logits);
+            prof_close(m, st);
             LAUNCH_CHECK();
         }
         return KDL_OK;
@@ -558,6 +615,7 @@ extern "C" int kdl_destroy(KdlModel *m) {
         if (m->h_meta[i]) { cudaFreeHost(m->h_meta[i]); cudaEventDestroy(m->slot_ev[i]); }
     }
     if (m->own_stream) cudaStreamDestroy(m->own_stream);
+    for (cudaEvent_t e : m->ev_pool) cudaEventDestroy(e);
     delete m;
     return KDL_OK;
 }
@@ -619,7 +677,9 @@ extern "C" int kdl_preprocess_u8(KdlModel *m, const uint8_t *d_src, const int64_
     if ((rc = stage_meta(m, offset, h, w, pitch, B, st, &dm))) return rc;
     int S = m->cfg.input_size;
     long long total = (long long)B * S * S * 3;
+    prof_open(m, st, PC_RESIZE, 0.0, 5.0 * total);
     k_resize<float><<<(unsigned)((total / 4 + 256) / 256), 256, 0, st>>>(d_src, dm, m->d_xtab, m->d_ytab, B, S, d_out);
+    prof_close(m, st);
     LAUNCH_CHECK();
     return KDL_OK;
 }
@@ -654,7 +714,9 @@ extern "C" int kdl_predict_u8(KdlModel *m, const uint8_t *d_src, const int64_t *
     int S = m->cfg.input_size;
     long long total = (long long)B * S * S * 3;
     // resized uint8 stays 1 byte/px; the x/127.5-1 scaling is applied (bit-exactly) inside block1_conv1's load
+    prof_open(m, st, PC_RESIZE, 0.0, 2.0 * total);
     k_resize<uint8_t><<<(unsigned)((total / 4 + 256) / 256), 256, 0, st>>>(d_src, dm, m->d_xtab, m->d_ytab, B, S, m->u8img);
+    prof_close(m, st);
     LAUNCH_CHECK();
     return run_forward(m, nullptr, m->u8img, B, d_dense_7, st);
 }
@@ -754,4 +816,45 @@ extern "C" int kdl_gemm_bf16(const void *d_A, const void *d_Wt, const float *d_b
     (void)err;
     return tc::launch_gemm(enc, (const bf16 *)d_A, (const bf16 *)d_Wt, &tmB, d_bias, (const bf16 *)d_residual, (bf16 *)d_out, M, N, K,
                            relu, (cudaStream_t)stream, g_err);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// per-launch profiling with CUDA events on the launching stream
+// ---------------------------------------------------------------------------------------------------
+extern "C" int kdl_profile_begin(KdlModel *m) {
+    if (!m) { set_err(g_err, "kdl_profile_begin: null model"); return KDL_EINVAL; }
+    m->profiling = true;
+    m->prof_recs.clear();
+    m->ev_used = 0;
+    for (int i = 0; i < 16; ++i) { m->cls_flops[i] = 0; m->cls_bytes[i] = 0; m->cls_launches[i] = 0; }
+    return KDL_OK;
+}
+
+extern "C" int kdl_profile_end(KdlModel *m, KdlProfileRow *rows, int32_t capacity, int32_t *n_rows) {
+    if (!m || !rows || !n_rows) { set_err(g_err, "kdl_profile_end: null argument"); return KDL_EINVAL; }
+    char *err = m->err;
+    m->profiling = false;
+    CK(cudaSetDevice(m->cfg.device));
+    CK(cudaDeviceSynchronize());
+    double ms[16] = {0};
+    for (auto &r : m->prof_recs) {
+        float t = 0.f;
+        CK(cudaEventElapsedTime(&t, r.a, r.b));
+        ms[r.cls] += t;
+    }
+    int n = 0;
+    for (int c = 0; c < PC_COUNT && n < capacity; ++c) {
+        if (!m->cls_launches[c]) continue;
+        KdlProfileRow &o = rows[n++];
+        memset(&o, 0, sizeof o);
+        strncpy(o.name, PROF_NAMES[c], sizeof(o.name) - 1);
+        o.launches = m->cls_launches[c];
+        o.ms = ms[c];
+        o.flops = m->cls_flops[c];
+        o.bytes = m->cls_bytes[c];
+    }
+    *n_rows = n;
+    m->prof_recs.clear();
+    m->ev_used = 0;
+    return KDL_OK;
 }

@@ -170,6 +170,17 @@ class Model:
             outs.append(self.predict_packed_host(PackedImages(images[i:i + self.max_batch])))
         return np.concatenate(outs, 0) if outs else np.empty((0, 10), np.float32)
 
+    def profile_begin(self):
+        """Bracket every kernel launch of this model with CUDA events (on the launching stream) until profile_end."""
+        _lib.check(self.lib.kdl_profile_begin(self.h), self.h)
+
+    def profile_end(self) -> List[dict]:
+        rows = (_lib.KdlProfileRow * 16)()
+        n = ctypes.c_int32()
+        _lib.check(self.lib.kdl_profile_end(self.h, rows, 16, ctypes.byref(n)), self.h)
+        return [{"kernel": rows[i].name.decode(), "launches": rows[i].launches, "ms": float(rows[i].ms),
+                 "flops": rows[i].flops, "bytes": rows[i].bytes} for i in range(n.value)]
+
     # ------------------------------------------------------------------------------------------
     def tap_names(self) -> List[str]:
         return [self.lib.kdl_tap_name(self.h, i).decode() for i in range(self.lib.kdl_num_taps(self.h))]
