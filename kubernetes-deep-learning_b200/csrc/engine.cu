@@ -236,7 +236,7 @@ template <typename T> struct Runner {
         const double bytes = ((double)M * g.K + (double)M * g.N * (resid ? 2 : 1) + (double)g.K * g.N) * sizeof(T) + 4.0 * g.N;
         if (use_tc() && rm.mode == 0 && tc::shape_supported(M, g.N, g.K)) {
             prof_open(m, st, g.K >= 512 ? PC_PW_TC_TENSOR : PC_PW_TC_HBM, flops, bytes);
-            int rc = tc::launch_gemm(m->tma, (const bf16 *)A, g.Wnk, &g.tmB, g.bias, (const bf16 *)resid, (bf16 *)out,
+            int rc = tc::launch_gemm(m->tma, (const bf16 *)A, &g.tmB, g.bias, (const bf16 *)resid, (bf16 *)out,
                                      M, g.N, g.K, relu, st, m->err);
             prof_close(m, st);
             if (rc != KDL_OK) return rc;
@@ -300,8 +300,17 @@ template <typename T> struct Runner {
             prof_close(m, st);
             LAUNCH_CHECK();
             RUN(tap("block1_conv1_act", U, sp[1], 32, 1));
-            // block1_conv2 as an implicit GEMM (K = 288)
-            RUN(gemm(U, m->conv2, nullptr, X, B * sp[2] * sp[2], 1, RowMap{2, sp[1], sp[1], sp[2], sp[2], 32}));
+            // block1_conv2 as an implicit GEMM (K = 9 taps x 32 channels)
+            if (use_tc()) {
+                prof_open(m, st, PC_CONV2, 2.0 * B * sp[2] * sp[2] * 288.0 * 64.0,
+                          ((double)B * sp[1] * sp[1] * 32 + (double)B * sp[2] * sp[2] * 64 + 288.0 * 64) * 2.0);
+                int rc = tc::launch_conv3x3(m->tma, (const bf16 *)U, &m->conv2.tmB, m->conv2.bias, (bf16 *)X, B, sp[1], sp[1], 1, st, m->err);
+                prof_close(m, st);
+                if (rc != KDL_OK) return rc;
+                m->launches++;
+            } else {
+                RUN(gemm(U, m->conv2, nullptr, X, B * sp[2] * sp[2], 1, RowMap{2, sp[1], sp[1], sp[2], sp[2], 32}));
+            }
             RUN(tap("block1_conv2_act", X, sp[2], 64, 1));
         }
         // ---- entry/exit blocks with projection + pool: 2,3,4 then middle, then 13 ----
@@ -421,7 +430,8 @@ static int upload(KdlModel *m, void **dst, const void *src, size_t bytes) {
 }
 
 // kernel [K][N] fp32 (Keras (kh,kw,cin,cout) flattened) + BN -> GemmW
-static int make_gemm(KdlModel *m, GemmW &g, const float *kern, int K, int N, const BnFold *bn, const float *bias) {
+static int make_gemm(KdlModel *m, GemmW &g, const float *kern, int K, int N, const BnFold *bn, const float *bias,
+                     bool conv3x3 = false) {
     g.K = K; g.N = N;
     std::vector<float> w((size_t)K * N);
     for (int k = 0; k < K; ++k)
@@ -445,7 +455,9 @@ static int make_gemm(KdlModel *m, GemmW &g, const float *kern, int K, int N, con
     rc = upload(m, (void **)&g.Wnk, wnk.data(), wnk.size() * 2);
     if (rc) return rc;
     if (m->tma.ok()) {
-        if (!m->tma.encode_2d(&g.tmB, g.Wnk, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, tc::BLOCK_K, tc::BLOCK_N)) {
+        bool ok = conv3x3 ? m->tma.encode_2d(&g.tmB, g.Wnk, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, 32, 64, 64)
+                          : m->tma.encode_2d(&g.tmB, g.Wnk, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, tc::BLOCK_K, tc::BLOCK_N, 128);
+        if (!ok) {
             set_err(m->err, "cuTensorMapEncodeTiled failed for weight [%d,%d]", N, K);
             return KDL_ECUDA;
         }
@@ -477,7 +489,7 @@ extern "C" int kdl_load_weights(KdlModel *m, const float *blob, size_t n_floats)
     {
         const float *k = p; p += 288 * 64;
         BnFold f = fold_bn(p, 64);
-        if ((rc = make_gemm(m, m->conv2, k, 288, 64, &f, nullptr))) return rc;
+        if ((rc = make_gemm(m, m->conv2, k, 288, 64, &f, nullptr, true))) return rc;
     }
     auto seps = sep_specs();
     m->dw.assign(seps.size(), nullptr);
@@ -809,13 +821,13 @@ extern "C" int kdl_gemm_bf16(const void *d_A, const void *d_Wt, const float *d_b
     int rc = tc::configure(g_err);
     if (rc) return rc;
     CUtensorMap tmB;
-    if (!enc.encode_2d(&tmB, d_Wt, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, tc::BLOCK_K, tc::BLOCK_N)) {
+    if (!enc.encode_2d(&tmB, d_Wt, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, tc::BLOCK_K, tc::BLOCK_N, 128)) {
         set_err(g_err, "kdl_gemm_bf16: tensor map encode failed");
         return KDL_ECUDA;
     }
     (void)err;
-    return tc::launch_gemm(enc, (const bf16 *)d_A, (const bf16 *)d_Wt, &tmB, d_bias, (const bf16 *)d_residual, (bf16 *)d_out, M, N, K,
-                           relu, (cudaStream_t)stream, g_err);
+    return tc::launch_gemm(enc, (const bf16 *)d_A, &tmB, d_bias, (const bf16 *)d_residual, (bf16 *)d_out, M, N, K, relu,
+                           (cudaStream_t)stream, g_err);
 }
 
 // ---------------------------------------------------------------------------------------------------

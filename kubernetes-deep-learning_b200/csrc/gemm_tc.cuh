@@ -1,14 +1,17 @@
-// K5: pointwise-convolution GEMM on the 5th-gen tensor cores (sm_100a), hand-written PTX:
-//   out[M,N] = act( A[M,K] * Wt[N,K]^T + bias[N] ) (+ residual[M,N]),  bf16 in / fp32 accumulate / bf16 out.
+// K5 / K3: GEMM-class layers on the 5th-gen tensor cores (sm_100a), hand-written PTX.
 //
-//   * operands staged by TMA (cp.async.bulk.tensor.2d, 128-byte swizzle) into a 4-stage shared-memory ring,
+//   pointwise / projection / (later) dense:  out[M,N] = act( A[M,K] * Wt[N,K]^T + bias[N] ) (+ residual[M,N])
+//   block1_conv2 (3x3, s1, VALID, 32->64) :  the same kernel in implicit-GEMM mode -- K = 9 taps x 32 channels, the A tile
+//                                            of tap (ky,kx) is the activation matrix shifted by ky*W+kx rows.
+//   bf16 operands, fp32 accumulation in TMEM, bf16 output.
+//
+//   * operands staged by TMA (cp.async.bulk.tensor.2d, 128- or 64-byte swizzle) into a shared-memory ring,
 //   * tcgen05.mma.cta_group::1.kind::f16 (M=128, N<=256, K=16 per instruction) issued by one elected thread,
-//   * fp32 accumulators live in TMEM (2 x 256 columns, double buffered so the epilogue of tile i overlaps
-//     the MMAs of tile i+1), read back with tcgen05.ld.32x32b,
+//   * accumulators double-buffered in TMEM so the epilogue of tile i overlaps the MMAs of tile i+1,
 //   * warp-specialised persistent CTAs (one per SM): warp 0 = TMA producer, warp 1 = MMA issuer + TMEM owner,
-//     warps 2..5 = epilogue (bias = folded BatchNorm shift, optional ReLU, optional residual add, bf16 store),
-//   * ragged shapes (C = 728 is neither a multiple of 16 nor of any legal N tile): the K tail and the N / M
-//     tails are zero-filled by TMA out-of-bounds handling and clipped in the epilogue; no padded copies.
+//     warps 2..5 = epilogue: tcgen05.ld -> +bias (folded BatchNorm shift, staged in smem once per tile) -> ReLU ->
+//     +residual (prefetched one chunk ahead) -> bf16 -> swizzled smem -> TMA store (clipped at the tensor edge),
+//   * ragged shapes (C = 728): K / N / M tails are zero-filled by TMA out-of-bounds handling and clipped on store.
 #pragma once
 #include <cuda.h>
 #include <cuda_runtime.h>
@@ -25,16 +28,33 @@ namespace kdl {
 namespace tc {
 
 constexpr int BLOCK_M = 128;
-constexpr int BLOCK_N = 256;
-constexpr int BLOCK_K = 64;  // 64 bf16 = 128 bytes = one swizzle-128B row
-constexpr int STAGES = 4;
 constexpr int UMMA_K = 16;
 constexpr int NUM_THREADS = 192;
-constexpr uint32_t A_BYTES = BLOCK_M * BLOCK_K * 2;  // 16 KB
-constexpr uint32_t B_BYTES = BLOCK_N * BLOCK_K * 2;  // 32 KB
-constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
-constexpr uint32_t SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
-constexpr uint32_t TMEM_COLS = 512;
+constexpr int BLOCK_N = 256;  // standard configuration (weight tensor-map box rows)
+constexpr int BLOCK_K = 64;   // standard configuration: 64 bf16 = 128 bytes = one swizzle-128B row
+
+template <int SW, int BN, bool CONV> struct Cfg {
+    static constexpr int BLOCK_N = BN;
+    static constexpr int BLOCK_K = SW / 2;  // elements per k-block = one swizzle row
+    static constexpr int STAGES = CONV ? 8 : 4;
+    static constexpr uint32_t A_BYTES = BLOCK_M * SW;
+    static constexpr uint32_t B_BYTES = BN * SW;
+    static constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr uint32_t EPI_BYTES = CONV ? 0 : 4 * 2 * 4096;  // per epilogue warp: 2 x (32 rows x 128 B)
+    static constexpr uint32_t BIAS_BYTES = BN * 4;
+    static constexpr uint32_t BAR_BYTES = 256;
+    static constexpr uint32_t SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BIAS_BYTES + BAR_BYTES + 1024 /*align slack*/;
+    static constexpr uint32_t TMEM_COLS = 2 * BN <= 32 ? 32 : 2 * BN <= 64 ? 64 : 2 * BN <= 128 ? 128 : 2 * BN <= 256 ? 256 : 512;
+    static_assert(SMEM_BYTES <= 232448, "exceeds 227 KB of shared memory per CTA");
+    static_assert(2 * BN <= 512, "two accumulators must fit the 512 TMEM columns");
+};
+typedef Cfg<128, 256, false> CfgStd;
+typedef Cfg<64, 64, true> CfgConv;
+
+// geometry of the implicit-GEMM conv mode (ignored otherwise)
+struct ConvGeom {
+    int Hin, Win, Hout, Wout;
+};
 
 // ---------------------------------------------------------------------------------------------------
 // host: TMA descriptor encoder (driver entry point fetched at run time; no link-time libcuda dependency)
@@ -55,17 +75,17 @@ struct TmaEncoder {
             (void)cudaGetLastError();
     }
     bool ok() const { return fn != nullptr; }
-    // row-major bf16 matrix [rows, cols] with `pitch_bytes` per row; box = box_cols x box_rows, 128B swizzle,
-    // out-of-bounds elements read as zero.
+    // row-major bf16 matrix [rows, cols] with `pitch_bytes` per row; box = box_cols x box_rows; swizzle 128 or 64 bytes
+    // (box_cols * 2 must equal the swizzle span); out-of-bounds elements read as zero / are not written.
     bool encode_2d(CUtensorMap *tm, const void *base, uint64_t cols, uint64_t rows, uint64_t pitch_bytes, uint32_t box_cols,
-                   uint32_t box_rows) const {
+                   uint32_t box_rows, int swizzle = 128) const {
         cuuint64_t dims[2] = {cols, rows};
         cuuint64_t strides[1] = {pitch_bytes};
         cuuint32_t box[2] = {box_cols, box_rows};
         cuuint32_t estr[2] = {1, 1};
         CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), dims, strides, box, estr,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         return r == CUDA_SUCCESS;
     }
 };
@@ -110,12 +130,28 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     }
 }
 __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
 
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *tm, uint32_t bar, int c0, int c1) {
     asm volatile(
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
         "l"(tm), "r"(bar), "r"(c0), "r"(c1)
         : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap *tm, uint32_t src, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(tm), "r"(src), "r"(c0),
+                 "r"(c1)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void bulk_wait_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+template <int N> __device__ __forceinline__ void bulk_wait_all() {
+    asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
 }
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap *tm) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(tm) : "memory");
@@ -145,7 +181,7 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
 
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t *r) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
         "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
@@ -159,17 +195,17 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
-// Shared-memory matrix descriptor: K-major operand tile written by TMA with 128-byte swizzle.
+// Shared-memory matrix descriptor: K-major operand tile written by TMA with SW-byte swizzle (rows of SW bytes).
 //   bits [0,14)  start address >> 4          bits [16,30) leading byte offset >> 4 (unused for swizzled K-major: 1)
-//   bits [32,46) stride byte offset >> 4 = 1024 B between 8-row groups      bits [46,48) descriptor version = 1 (sm_100)
-//   bits [61,64) layout type: 2 = SWIZZLE_128B
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr) {
+//   bits [32,46) stride byte offset >> 4 = 8 rows * SW bytes between 8-row groups
+//   bits [46,48) descriptor version = 1 (sm_100)       bits [61,64) layout type: 2 = SWIZZLE_128B, 4 = SWIZZLE_64B
+template <int SW> __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr) {
     uint64_t d = 0;
     d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
     d |= (uint64_t)1 << 16;
-    d |= (uint64_t)(1024 >> 4) << 32;
+    d |= (uint64_t)((8 * SW) >> 4) << 32;
     d |= (uint64_t)1 << 46;
-    d |= (uint64_t)2 << 61;
+    d |= (uint64_t)(SW == 128 ? 2 : 4) << 61;
     return d;
 }
 // Instruction descriptor for kind::f16: D = F32 (bits 4-5 = 1), A = B = BF16 (bits 7-9, 10-12 = 1), both K-major
@@ -182,16 +218,55 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
     __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
     return *reinterpret_cast<uint32_t *>(&v);
 }
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint4 v) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ float4 ld_shared_f4(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+
+// bias (+ReLU) (+residual) on 8 accumulator columns -> one 16-byte bf16 vector
+__device__ __forceinline__ uint4 epi8(const uint32_t *acc, uint32_t bias_addr, int relu, bool has_res, uint4 rr) {
+    const float4 b0 = ld_shared_f4(bias_addr), b1 = ld_shared_f4(bias_addr + 16);
+    float v[8];
+    v[0] = __uint_as_float(acc[0]) + b0.x; v[1] = __uint_as_float(acc[1]) + b0.y;
+    v[2] = __uint_as_float(acc[2]) + b0.z; v[3] = __uint_as_float(acc[3]) + b0.w;
+    v[4] = __uint_as_float(acc[4]) + b1.x; v[5] = __uint_as_float(acc[5]) + b1.y;
+    v[6] = __uint_as_float(acc[6]) + b1.z; v[7] = __uint_as_float(acc[7]) + b1.w;
+    if (relu) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
+    }
+    if (has_res) {
+        v[0] += __uint_as_float(rr.x << 16); v[1] += __uint_as_float(rr.x & 0xffff0000u);
+        v[2] += __uint_as_float(rr.y << 16); v[3] += __uint_as_float(rr.y & 0xffff0000u);
+        v[4] += __uint_as_float(rr.z << 16); v[5] += __uint_as_float(rr.z & 0xffff0000u);
+        v[6] += __uint_as_float(rr.w << 16); v[7] += __uint_as_float(rr.w & 0xffff0000u);
+    }
+    uint4 o;
+    o.x = pack_bf16(v[0], v[1]); o.y = pack_bf16(v[2], v[3]);
+    o.z = pack_bf16(v[4], v[5]); o.w = pack_bf16(v[6], v[7]);
+    return o;
+}
 
 // ---------------------------------------------------------------------------------------------------
 // the kernel
 // ---------------------------------------------------------------------------------------------------
+template <int SW, int BN, bool CONV>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
-k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const float *__restrict__ bias,
-          const bf16 *residual, bf16 *out, int M, int N, int K, int relu) {
+k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+          const __grid_constant__ CUtensorMap tmOut, const float *__restrict__ bias, const bf16 *residual, bf16 *out, int M,
+          int N, int K, int relu, ConvGeom cg) {
+    typedef Cfg<SW, BN, CONV> C;
+    constexpr int STAGES = C::STAGES;
+    constexpr int BK = C::BLOCK_K;
     extern __shared__ uint8_t smem_raw[];
-    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // swizzle-128B tiles need 1024-byte alignment
-    const uint32_t bar_base = smem_base + STAGES * STAGE_BYTES;
+    const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // swizzled tiles need 1024-byte alignment
+    const uint32_t epi_base = smem_base + STAGES * C::STAGE_BYTES;
+    const uint32_t bias_base = epi_base + C::EPI_BYTES;
+    const uint32_t bar_base = bias_base + C::BIAS_BYTES;
     // barrier slots (8 B each): full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2]; then the TMEM base address
     auto full_bar = [&](int s) { return bar_base + 8u * s; };
     auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
@@ -202,18 +277,19 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int m_tiles = (M + BLOCK_M - 1) / BLOCK_M;
-    const int n_tiles = (N + BLOCK_N - 1) / BLOCK_N;
+    const int n_tiles = (N + BN - 1) / BN;
     const int num_tiles = m_tiles * n_tiles;
-    const int k_blocks = (K + BLOCK_K - 1) / BLOCK_K;
+    const int k_blocks = (K + BK - 1) / BK;
 
     if (warp == 0 && lane == 0) {
         prefetch_tmap(&tmA);
         prefetch_tmap(&tmB);
+        if (!CONV) prefetch_tmap(&tmOut);
         for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
         for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4); }
         fence_barrier_init();
     }
-    if (warp == 1) tmem_alloc(tmem_slot, TMEM_COLS);
+    if (warp == 1) tmem_alloc(tmem_slot, C::TMEM_COLS);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -226,13 +302,18 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             int stage = 0;
             uint32_t phase = 0;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-                const int m0 = (tile / n_tiles) * BLOCK_M, n0 = (tile % n_tiles) * BLOCK_N;
+                const int m0 = (tile / n_tiles) * BLOCK_M, n0 = (tile % n_tiles) * BN;
                 for (int kb = 0; kb < k_blocks; ++kb) {
                     mbar_wait(empty_bar(stage), phase ^ 1u);
-                    mbar_expect_tx(full_bar(stage), STAGE_BYTES);
-                    const uint32_t sa = smem_base + stage * STAGE_BYTES;
-                    tma_load_2d(sa, &tmA, full_bar(stage), kb * BLOCK_K, m0);
-                    tma_load_2d(sa + A_BYTES, &tmB, full_bar(stage), kb * BLOCK_K, n0);
+                    mbar_expect_tx(full_bar(stage), C::STAGE_BYTES);
+                    const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
+                    if (CONV) {
+                        // tap kb = (ky,kx): the activation matrix [B*Hin*Win, Cin] shifted by ky*Win + kx rows
+                        tma_load_2d(sa, &tmA, full_bar(stage), 0, m0 + (kb / 3) * cg.Win + (kb % 3));
+                    } else {
+                        tma_load_2d(sa, &tmA, full_bar(stage), kb * BK, m0);
+                    }
+                    tma_load_2d(sa + C::A_BYTES, &tmB, full_bar(stage), kb * BK, n0);
                     if (++stage == STAGES) { stage = 0; phase ^= 1u; }
                 }
             }
@@ -244,25 +325,25 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             uint32_t phase = 0;
             int it = 0;
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-                const int n0 = (tile % n_tiles) * BLOCK_N;
+                const int n0 = (tile % n_tiles) * BN;
                 const int acc = it & 1;
                 const uint32_t acc_phase = (it >> 1) & 1;
                 // shrink the instruction to the valid part of a ragged N tile (multiple of 16)
-                int n_valid = min(BLOCK_N, N - n0);
+                const int n_valid = min(BN, N - n0);
                 const uint32_t idesc = make_idesc(BLOCK_M, (uint32_t)((n_valid + 15) & ~15));
                 mbar_wait(tempty_bar(acc), acc_phase ^ 1u);  // epilogue has drained this accumulator
                 tc_fence_after();
-                const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
+                const uint32_t d_tmem = tmem_base + acc * BN;
                 for (int kb = 0; kb < k_blocks; ++kb) {
                     mbar_wait(full_bar(stage), phase);
                     tc_fence_after();
-                    const uint32_t sa = smem_base + stage * STAGE_BYTES;
-                    const uint64_t adesc = make_smem_desc(sa);
-                    const uint64_t bdesc = make_smem_desc(sa + A_BYTES);
-                    const int k_left = K - kb * BLOCK_K;
-                    const int ksteps = k_left >= BLOCK_K ? BLOCK_K / UMMA_K : (k_left + UMMA_K - 1) / UMMA_K;
+                    const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
+                    const uint64_t adesc = make_smem_desc<SW>(sa);
+                    const uint64_t bdesc = make_smem_desc<SW>(sa + C::A_BYTES);
+                    const int k_left = K - kb * BK;
+                    const int ksteps = k_left >= BK ? BK / UMMA_K : (k_left + UMMA_K - 1) / UMMA_K;
                     for (int k = 0; k < ksteps; ++k) {
-                        // advance 16 elements = 32 bytes inside the swizzle atom: +2 in the (addr >> 4) field
+                        // advance 16 elements = 32 bytes inside the swizzle row: +2 in the (addr >> 4) field
                         umma_bf16(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (kb | k) != 0);
                     }
                     umma_commit(empty_bar(stage));  // frees the smem stage when these MMAs have read it
@@ -274,51 +355,83 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     } else {
         // ================= epilogue: warps 2..5; TMEM lane quarter = warp % 4 =================
         const int q = warp & 3;
+        const int et = threadIdx.x - 64;  // 0..127
+        const uint32_t ebuf = epi_base + (uint32_t)(warp - 2) * 8192u;
+        const bool has_res = residual != nullptr;
         int it = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
-            const int m0 = (tile / n_tiles) * BLOCK_M, n0 = (tile % n_tiles) * BLOCK_N;
+            const int m0 = (tile / n_tiles) * BLOCK_M, n0 = (tile % n_tiles) * BN;
             const int acc = it & 1;
             const uint32_t acc_phase = (it >> 1) & 1;
-            mbar_wait(tfull_bar(acc), acc_phase);
-            tc_fence_after();
-            const int row = m0 + q * 32 + lane;
-            const bool row_ok = row < M;
-            const uint32_t t_row = tmem_base + acc * BLOCK_N + ((uint32_t)(q * 32) << 16);
-            const size_t row_off = (size_t)row * N;
-#pragma unroll 1
-            for (int c = 0; c < BLOCK_N / 32; ++c) {
-                const int nc = n0 + c * 32;
-                if (nc >= N) break;  // warp-uniform
-                uint32_t r[32];
-                tmem_ld32(t_row + c * 32, r);
+            // stage this tile's bias slice once (all four epilogue warps share it)
+            named_bar_sync(1, 128);
+            for (int j = et; j < BN; j += 128) {
+                float b = (n0 + j < N) ? __ldg(bias + n0 + j) : 0.f;
+                asm volatile("st.shared.f32 [%0], %1;" ::"r"(bias_base + 4u * j), "f"(b) : "memory");
+            }
+            named_bar_sync(1, 128);
+            const int row0 = m0 + q * 32;
+            const int row = row0 + lane;
+            const uint32_t t_row = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
+            if (CONV) {
+                // ---- implicit-GEMM conv: row = input-grid position (b,y,x); valid outputs have y < Hout, x < Wout ----
+                mbar_wait(tfull_bar(acc), acc_phase);
+                tc_fence_after();
+                uint32_t r[64];
+                tmem_ld32(t_row, r);
+                tmem_ld32(t_row + 32, r + 32);
                 tmem_ld_wait();
-                if (row_ok) {
+                const int hw = cg.Hin * cg.Win;
+                const int b = row / hw;
+                const int rem = row - b * hw;
+                const int y = rem / cg.Win, x = rem - y * cg.Win;
+                if (row < M && y < cg.Hout && x < cg.Wout) {
+                    bf16 *o = out + ((size_t)(b * cg.Hout + y) * cg.Wout + x) * N + n0;
 #pragma unroll
-                    for (int g = 0; g < 4; ++g) {  // 8 columns = one 16-byte bf16 vector
-                        const int n = nc + g * 8;
-                        if (n < N) {
-                            const float4 b0 = __ldg(reinterpret_cast<const float4 *>(bias + n));
-                            const float4 b1 = __ldg(reinterpret_cast<const float4 *>(bias + n + 4));
-                            float v[8];
-                            v[0] = __uint_as_float(r[g * 8 + 0]) + b0.x; v[1] = __uint_as_float(r[g * 8 + 1]) + b0.y;
-                            v[2] = __uint_as_float(r[g * 8 + 2]) + b0.z; v[3] = __uint_as_float(r[g * 8 + 3]) + b0.w;
-                            v[4] = __uint_as_float(r[g * 8 + 4]) + b1.x; v[5] = __uint_as_float(r[g * 8 + 5]) + b1.y;
-                            v[6] = __uint_as_float(r[g * 8 + 6]) + b1.z; v[7] = __uint_as_float(r[g * 8 + 7]) + b1.w;
-                            if (relu) {
+                    for (int g = 0; g < 8; ++g)
+                        *reinterpret_cast<uint4 *>(o + g * 8) = epi8(r + g * 8, bias_base + 32u * g, relu, false, make_uint4(0, 0, 0, 0));
+                }
+            } else {
+                // ---- standard: 64-column chunks -> swizzled smem -> TMA store; residual prefetched a chunk ahead ----
+                const bool row_ok = row < M;
+                const bf16 *res_row = residual + (size_t)row * N;
+                uint4 rn[8];
+                auto load_res = [&](int c) {
 #pragma unroll
-                                for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
-                            }
-                            if (residual) {
-                                const uint4 rr = *reinterpret_cast<const uint4 *>(residual + row_off + n);
-                                v[0] += __uint_as_float(rr.x << 16); v[1] += __uint_as_float(rr.x & 0xffff0000u);
-                                v[2] += __uint_as_float(rr.y << 16); v[3] += __uint_as_float(rr.y & 0xffff0000u);
-                                v[4] += __uint_as_float(rr.z << 16); v[5] += __uint_as_float(rr.z & 0xffff0000u);
-                                v[6] += __uint_as_float(rr.w << 16); v[7] += __uint_as_float(rr.w & 0xffff0000u);
-                            }
-                            uint4 o;
-                            o.x = pack_bf16(v[0], v[1]); o.y = pack_bf16(v[2], v[3]);
-                            o.z = pack_bf16(v[4], v[5]); o.w = pack_bf16(v[6], v[7]);
-                            *reinterpret_cast<uint4 *>(out + row_off + n) = o;
+                    for (int g = 0; g < 8; ++g) {
+                        const int n = n0 + c * 64 + g * 8;
+                        rn[g] = (has_res && row_ok && n < N) ? *reinterpret_cast<const uint4 *>(res_row + n) : make_uint4(0, 0, 0, 0);
+                    }
+                };
+                if (has_res) load_res(0);
+                mbar_wait(tfull_bar(acc), acc_phase);
+                tc_fence_after();
+#pragma unroll
+                for (int c = 0; c < BN / 64; ++c) {
+                    const int nc = n0 + c * 64;
+                    if (nc < N) {  // warp-uniform
+                        uint32_t r[64];
+                        tmem_ld32(t_row + c * 64, r);
+                        tmem_ld32(t_row + c * 64 + 32, r + 32);
+                        uint4 rc[8];
+#pragma unroll
+                        for (int g = 0; g < 8; ++g) rc[g] = rn[g];
+                        if (has_res && c + 1 < BN / 64 && nc + 64 < N) load_res(c + 1);
+                        const uint32_t buf = ebuf + (uint32_t)(c & 1) * 4096u;
+                        // the TMA store issued two chunks ago from this buffer must have finished reading it
+                        if (lane == 0) bulk_wait_read<1>();
+                        __syncwarp();
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int g = 0; g < 8; ++g) {
+                            const uint4 o = epi8(r + g * 8, bias_base + (uint32_t)(c * 64 + g * 8) * 4u, relu, has_res, rc[g]);
+                            st_shared_v4(buf + (uint32_t)lane * 128u + (uint32_t)((g ^ (lane & 7)) << 4), o);
+                        }
+                        fence_proxy_async_smem();
+                        __syncwarp();
+                        if (lane == 0 && row0 < M) {
+                            tma_store_2d(&tmOut, buf, nc, row0);
+                            bulk_commit();
                         }
                     }
                 }
@@ -327,12 +440,13 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty_bar(acc));
         }
+        if (!CONV && lane == 0) bulk_wait_all<0>();
     }
     tc_fence_before();
     __syncthreads();
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, TMEM_COLS);
+        tmem_dealloc(tmem_base, C::TMEM_COLS);
     }
 }
 
@@ -340,9 +454,12 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
 // host launch
 // ---------------------------------------------------------------------------------------------------
 inline int configure(char *err) {
-    cudaError_t e = cudaFuncSetAttribute(k_gemm_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
+    cudaError_t e = cudaFuncSetAttribute(k_gemm_tc<128, 256, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)CfgStd::SMEM_BYTES);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(k_gemm_tc<64, 64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CfgConv::SMEM_BYTES);
     if (e != cudaSuccess) {
-        snprintf(err, 512, "cudaFuncSetAttribute(k_gemm_tc, %u B smem): %s", SMEM_BYTES, cudaGetErrorString(e));
+        snprintf(err, 512, "cudaFuncSetAttribute(k_gemm_tc smem): %s", cudaGetErrorString(e));
         return KDL_ECUDA;
     }
     return KDL_OK;
@@ -359,20 +476,45 @@ inline int num_sms() {
     return n;
 }
 
-inline int launch_gemm(const TmaEncoder &enc, const bf16 *A, const bf16 *Wt, const CUtensorMap *tmB, const float *bias,
-                       const bf16 *residual, bf16 *out, int M, int N, int K, int relu, cudaStream_t st, char *err) {
-    (void)Wt;
-    CUtensorMap tmA;
-    if (!enc.encode_2d(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)K * 2, BLOCK_K, BLOCK_M)) {
-        snprintf(err, 512, "cuTensorMapEncodeTiled failed for A [%d,%d]", M, K);
+// standard GEMM: A [M,K] bf16 row-major, weights via tmB (box BLOCK_K x BLOCK_N over Wt[N,K]), out [M,N]
+inline int launch_gemm(const TmaEncoder &enc, const bf16 *A, const CUtensorMap *tmB, const float *bias, const bf16 *residual,
+                       bf16 *out, int M, int N, int K, int relu, cudaStream_t st, char *err) {
+    CUtensorMap tmA, tmOut;
+    if (!enc.encode_2d(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)K * 2, BLOCK_K, BLOCK_M, 128) ||
+        !enc.encode_2d(&tmOut, out, (uint64_t)N, (uint64_t)M, (uint64_t)N * 2, 64, 32, 128)) {
+        snprintf(err, 512, "cuTensorMapEncodeTiled failed for A [%d,%d] / out [%d,%d]", M, K, M, N);
         return KDL_ECUDA;
     }
     const int tiles = ((M + BLOCK_M - 1) / BLOCK_M) * ((N + BLOCK_N - 1) / BLOCK_N);
     const int grid = tiles < num_sms() ? tiles : num_sms();
-    k_gemm_tc<<<grid, NUM_THREADS, SMEM_BYTES, st>>>(tmA, *tmB, bias, residual, out, M, N, K, relu);
+    k_gemm_tc<128, 256, false><<<grid, NUM_THREADS, CfgStd::SMEM_BYTES, st>>>(tmA, *tmB, tmOut, bias, residual, out, M, N, K, relu,
+                                                                              ConvGeom{0, 0, 0, 0});
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         snprintf(err, 512, "k_gemm_tc launch (M=%d N=%d K=%d): %s", M, N, K, cudaGetErrorString(e));
+        return KDL_ECUDA;
+    }
+    return KDL_OK;
+}
+
+// block1_conv2 as implicit GEMM: in [B,Hin,Win,32] bf16, weights via tmB (box 32 x 64 over Wt[64, 288], 64B swizzle),
+// out [B,Hout,Wout,64]
+inline int launch_conv3x3(const TmaEncoder &enc, const bf16 *in, const CUtensorMap *tmB, const float *bias, bf16 *out, int B, int Hin,
+                          int Win, int relu, cudaStream_t st, char *err) {
+    const int Cin = 32, Cout = 64;
+    const int M = B * Hin * Win;  // one GEMM row per input-grid position; the 2 rightmost / bottom positions are discarded
+    CUtensorMap tmA;
+    if (!enc.encode_2d(&tmA, in, Cin, (uint64_t)M, Cin * 2, 32, BLOCK_M, 64)) {
+        snprintf(err, 512, "cuTensorMapEncodeTiled failed for conv input [%d,%d]", M, Cin);
+        return KDL_ECUDA;
+    }
+    const int tiles = (M + BLOCK_M - 1) / BLOCK_M;
+    const int grid = tiles < num_sms() ? tiles : num_sms();
+    k_gemm_tc<64, 64, true><<<grid, NUM_THREADS, CfgConv::SMEM_BYTES, st>>>(tmA, *tmB, tmA /*unused*/, bias, nullptr, out, M, Cout,
+                                                                            9 * Cin, relu, ConvGeom{Hin, Win, Hin - 2, Win - 2});
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        snprintf(err, 512, "k_gemm_tc<conv> launch (B=%d H=%d): %s", B, Hin, cudaGetErrorString(e));
         return KDL_ECUDA;
     }
     return KDL_OK;
