@@ -1,0 +1,280 @@
+// K4 (bf16 path): depthwise 3x3 s1 SAME with TMA halo staging.  Memory-bound: the goal is HBM bandwidth.
+//
+//   * the NHWC activation is a 4-D tensor (C, W, H, B) for TMA; one tile = 64 channels x (TW+2) x (TH+2) pixels, fetched by a
+//     single cp.async.bulk.tensor.4d whose box starts at (x0-1, y0-1): the halo AND the SAME zero padding come from TMA's
+//     out-of-bounds fill (negative / past-the-edge coordinates read as 0), so the compute loop has no border branches,
+//   * persistent CTAs, 3-stage mbarrier ring, one producer warp; the 9x64 fp32 weights of the tile's channel chunk ride along in
+//     the same stage (cp.async.bulk), so consumers never touch global memory except for the coalesced output store,
+//   * each consumer thread owns 4 channels of 2 adjacent columns and walks down a strip of rows; every input row it loads
+//     (4 x LDS.64) is scattered into the three output rows it touches with packed FFMA2 (fma.rn.f32x2), fp32 accumulation,
+//   * optional ReLU on load (the residual tensor must stay un-rectified) as packed bf16x2 max.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include "common.cuh"
+#include "gemm_tc.cuh"  // mbarrier / TMA PTX wrappers
+
+namespace kdl {
+namespace dwt {
+
+constexpr int STAGES = 3;
+constexpr int CB = 64;                       // channels per tile
+constexpr uint32_t W_BYTES = 9 * CB * 4;     // fp32 weights of one chunk: [9][64]
+constexpr uint32_t TILE_BUDGET = 61440;      // max bytes of one staged input tile
+
+struct Params {
+    int B, H, W, C;
+    int TW, TH;      // output tile (pixels)
+    int BW;          // staged box width  = 2*CP + 2  (>= TW + 2)
+    int BH;          // staged box height = TH + 2
+    int CP;          // column pairs per tile
+    int NS, RS;      // row strips per tile and rows per strip
+    int ntx, nty, nch, total_tiles;
+    int relu_in;
+    uint32_t tile_bytes, stage_bytes;
+    int consumer_threads;
+};
+
+inline Params make_params(int B, int H, int W, int C, int relu_in) {
+    Params p;
+    p.B = B; p.H = H; p.W = W; p.C = C; p.relu_in = relu_in;
+    int ntx = (W + 36) / 37;
+    p.TW = (W + ntx - 1) / ntx;
+    p.ntx = ntx;
+    p.CP = (p.TW + 1) / 2;
+    p.BW = 2 * p.CP + 2;
+    int max_bh = (int)(TILE_BUDGET / (uint32_t)(p.BW * 128));
+    int th_max = max_bh - 2 < 1 ? 1 : max_bh - 2;
+    if (th_max > H) th_max = H;
+    p.nty = (H + th_max - 1) / th_max;
+    p.TH = (H + p.nty - 1) / p.nty;
+    p.BH = p.TH + 2;
+    int per_strip = 16 * p.CP;
+    int ns = 352 / per_strip;          // strips cost (RS+2)/RS extra row scatters: keep them >= 8 rows tall
+    if (ns > p.TH / 8) ns = p.TH / 8;
+    if (ns < 1) ns = 1;
+    p.RS = (p.TH + ns - 1) / ns;
+    p.NS = (p.TH + p.RS - 1) / p.RS;
+    p.consumer_threads = ((per_strip * p.NS + 31) / 32) * 32;
+    p.nch = (C + CB - 1) / CB;
+    p.total_tiles = B * p.nty * p.ntx * p.nch;
+    p.tile_bytes = (uint32_t)(p.BW * p.BH * 128);
+    p.stage_bytes = p.tile_bytes + W_BYTES;
+    return p;
+}
+inline uint32_t smem_bytes(const Params &p) { return STAGES * p.stage_bytes + 128 /*barriers*/ + 128 /*align*/; }
+
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap *tm, uint32_t bar, int c0, int c1, int c2, int c3) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(dst),
+        "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+        : "memory");
+}
+__device__ __forceinline__ void bulk_load_1d(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src),
+                 "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+    unsigned long long d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;"
+        : "=l"(d)
+        : "l"(*reinterpret_cast<unsigned long long *>(&a)), "l"(*reinterpret_cast<unsigned long long *>(&b)),
+          "l"(*reinterpret_cast<unsigned long long *>(&c)));
+    return *reinterpret_cast<float2 *>(&d);
+}
+__device__ __forceinline__ float2 fmul2(float2 a, float2 b) { return make_float2(a.x * b.x, a.y * b.y); }
+
+struct Px {  // 4 channels of one pixel in fp32
+    float2 lo, hi;
+};
+template <bool RELU> __device__ __forceinline__ Px ld_px(uint32_t addr) {
+    uint32_t a, b;
+    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(a), "=r"(b) : "r"(addr));
+    if (RELU) {  // packed bf16x2 max against +0
+        asm("max.bf16x2 %0, %0, %1;" : "+r"(a) : "r"(0u));
+        asm("max.bf16x2 %0, %0, %1;" : "+r"(b) : "r"(0u));
+    }
+    Px p;
+    p.lo = make_float2(__uint_as_float(a << 16), __uint_as_float(a & 0xffff0000u));
+    p.hi = make_float2(__uint_as_float(b << 16), __uint_as_float(b & 0xffff0000u));
+    return p;
+}
+
+template <bool RELU>
+__global__ void __launch_bounds__(384, 1)
+k_dw_tma(const __grid_constant__ CUtensorMap tmIn, const float *__restrict__ wpad /*[nch][9][64]*/, bf16 *__restrict__ out, Params p) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (tc::smem_u32(smem_raw) + 127u) & ~127u;
+    const uint32_t bar_base = base + STAGES * p.stage_bytes;
+    auto full_bar = [&](int s) { return bar_base + 8u * s; };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n_cwarps = p.consumer_threads >> 5;
+
+    if (threadIdx.x == 0) {
+        tc::prefetch_tmap(&tmIn);
+        for (int s = 0; s < STAGES; ++s) { tc::mbar_init(full_bar(s), 1); tc::mbar_init(empty_bar(s), n_cwarps); }
+        tc::fence_barrier_init();
+    }
+    __syncthreads();
+
+    if (warp == n_cwarps) {
+        // ================= producer warp =================
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
+                const int ch = t % p.nch;
+                int s = t / p.nch;
+                const int tx = s % p.ntx; s /= p.ntx;
+                const int ty = s % p.nty;
+                const int b = s / p.nty;
+                tc::mbar_wait(empty_bar(stage), phase ^ 1u);
+                tc::mbar_expect_tx(full_bar(stage), p.stage_bytes);
+                const uint32_t dst = base + stage * p.stage_bytes;
+                tma_load_4d(dst, &tmIn, full_bar(stage), ch * CB, tx * p.TW - 1, ty * p.TH - 1, b);
+                bulk_load_1d(dst + p.tile_bytes, wpad + (size_t)ch * 9 * CB, W_BYTES, full_bar(stage));
+                if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+            }
+        }
+        return;
+    }
+    if (warp > n_cwarps) return;
+
+    // ================= consumers =================
+    const int cg = threadIdx.x & 15;           // 4-channel group inside the 64-channel chunk
+    const int rest = threadIdx.x >> 4;
+    const int cp = rest % p.CP;                // column pair
+    const int strip = rest / p.CP;
+    const bool active = strip < p.NS;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
+        const int ch = t % p.nch;
+        int s = t / p.nch;
+        const int tx = s % p.ntx; s /= p.ntx;
+        const int ty = s % p.nty;
+        const int b = s / p.nty;
+        tc::mbar_wait(full_bar(stage), phase);
+        const int c = ch * CB + cg * 4;
+        const int x0 = tx * p.TW + 2 * cp;                 // first of this thread's two output columns
+        const int y_lo = strip * p.RS;                     // tile-relative first output row of the strip
+        int y_hi = min(y_lo + p.RS, p.TH);
+        y_hi = min(y_hi, p.H - ty * p.TH);                 // clip the last tile row
+        if (active && c < p.C && x0 < p.W && 2 * cp < p.TW && y_lo < y_hi) {
+            const uint32_t tile = base + stage * p.stage_bytes;
+            const uint32_t wb = tile + p.tile_bytes + (uint32_t)cg * 16u;
+            float2 wl[9], wh[9];
+#pragma unroll
+            for (int k = 0; k < 9; ++k) {
+                const float4 w4 = tc::ld_shared_f4(wb + (uint32_t)k * (CB * 4));
+                wl[k] = make_float2(w4.x, w4.y);
+                wh[k] = make_float2(w4.z, w4.w);
+            }
+            const bool st1 = (2 * cp + 1 < p.TW) && (x0 + 1 < p.W);
+            // points at output row y_lo - 1 (first store happens after the first increment)
+            bf16 *o = out + (((size_t)b * p.H + (size_t)ty * p.TH + y_lo) * p.W + x0) * p.C + c - (size_t)p.W * p.C;
+            const size_t orow = (size_t)p.W * p.C;
+            // accumulators of output rows (r-1, r, r+1) relative to the input row r being scattered; [col][lo/hi]
+            float2 aA[2][2], aB[2][2], aC[2][2];
+            const float2 z2 = make_float2(0.f, 0.f);
+#pragma unroll
+            for (int j = 0; j < 2; ++j) { aA[j][0] = aA[j][1] = aB[j][0] = aB[j][1] = z2; }
+            // staged row index = tile-relative input row + 1; thread's columns start at staged column 2*cp
+            uint32_t rowaddr = tile + ((uint32_t)(y_lo * p.BW) + 2u * cp) * 128u + (uint32_t)cg * 8u;
+            const uint32_t rowpitch = (uint32_t)p.BW * 128u;
+            for (int r = y_lo - 1; r <= y_hi; ++r, rowaddr += rowpitch) {
+                Px in[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) in[j] = ld_px<RELU>(rowaddr + 128u * j);
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    // bottom taps (ky = 2) complete output row r-1; middle taps (ky = 1) -> row r; top taps start row r+1
+                    float2 cl = fmul2(in[j].lo, wl[0]), chh = fmul2(in[j].hi, wh[0]);
+#pragma unroll
+                    for (int kx = 0; kx < 3; ++kx) {
+                        aA[j][0] = ffma2(in[j + kx].lo, wl[6 + kx], aA[j][0]);
+                        aA[j][1] = ffma2(in[j + kx].hi, wh[6 + kx], aA[j][1]);
+                        aB[j][0] = ffma2(in[j + kx].lo, wl[3 + kx], aB[j][0]);
+                        aB[j][1] = ffma2(in[j + kx].hi, wh[3 + kx], aB[j][1]);
+                        if (kx > 0) {
+                            cl = ffma2(in[j + kx].lo, wl[kx], cl);
+                            chh = ffma2(in[j + kx].hi, wh[kx], chh);
+                        }
+                    }
+                    aC[j][0] = cl;
+                    aC[j][1] = chh;
+                }
+                if (r > y_lo) {  // output row r-1 is complete
+                    uint2 v0, v1;
+                    v0.x = tc::pack_bf16(aA[0][0].x, aA[0][0].y); v0.y = tc::pack_bf16(aA[0][1].x, aA[0][1].y);
+                    v1.x = tc::pack_bf16(aA[1][0].x, aA[1][0].y); v1.y = tc::pack_bf16(aA[1][1].x, aA[1][1].y);
+                    *reinterpret_cast<uint2 *>(o) = v0;
+                    if (st1) *reinterpret_cast<uint2 *>(o + p.C) = v1;
+                }
+                if (r >= y_lo) o += orow;
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    aA[j][0] = aB[j][0]; aA[j][1] = aB[j][1];
+                    aB[j][0] = aC[j][0]; aB[j][1] = aC[j][1];
+                }
+            }
+        }
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(empty_bar(stage));
+        if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+    }
+}
+
+// host -------------------------------------------------------------------------------------------------
+typedef tc::EncodeTiledFn EncodeFn;
+
+inline bool encode_input_map(const tc::TmaEncoder &enc, CUtensorMap *tm, const void *in, const Params &p) {
+    cuuint64_t dims[4] = {(cuuint64_t)p.C, (cuuint64_t)p.W, (cuuint64_t)p.H, (cuuint64_t)p.B};
+    cuuint64_t strides[3] = {(cuuint64_t)p.C * 2, (cuuint64_t)p.W * p.C * 2, (cuuint64_t)p.H * p.W * p.C * 2};
+    cuuint32_t box[4] = {(cuuint32_t)CB, (cuuint32_t)p.BW, (cuuint32_t)p.BH, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    return enc.fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void *>(in), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+inline int configure(char *err) {
+    cudaError_t e = cudaFuncSetAttribute(k_dw_tma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * (int)(TILE_BUDGET + W_BYTES) + 256);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(k_dw_tma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * (int)(TILE_BUDGET + W_BYTES) + 256);
+    if (e != cudaSuccess) {
+        snprintf(err, 512, "cudaFuncSetAttribute(k_dw_tma): %s", cudaGetErrorString(e));
+        return KDL_ECUDA;
+    }
+    return KDL_OK;
+}
+
+inline int launch(const tc::TmaEncoder &enc, const bf16 *in, const float *wpad, bf16 *out, int B, int H, int W, int C, int relu_in,
+                  cudaStream_t st, char *err) {
+    Params p = make_params(B, H, W, C, relu_in);
+    CUtensorMap tm;
+    if (!encode_input_map(enc, &tm, in, p)) {
+        snprintf(err, 512, "cuTensorMapEncodeTiled(4d) failed for depthwise input [%d,%d,%d,%d] box [%d,%d]", B, H, W, C, p.BW, p.BH);
+        return KDL_ECUDA;
+    }
+    int per_sm = (int)(220u * 1024u / smem_bytes(p));
+    if (per_sm > 4) per_sm = 4;
+    if (per_sm < 1) per_sm = 1;
+    const int nsm = tc::num_sms() * per_sm;
+    const int grid = p.total_tiles < nsm ? p.total_tiles : nsm;
+    if (relu_in) k_dw_tma<true><<<grid, p.consumer_threads + 32, smem_bytes(p), st>>>(tm, wpad, out, p);
+    else k_dw_tma<false><<<grid, p.consumer_threads + 32, smem_bytes(p), st>>>(tm, wpad, out, p);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        snprintf(err, 512, "k_dw_tma launch (B=%d H=%d C=%d threads=%d smem=%u): %s", B, H, C, p.consumer_threads + 32, smem_bytes(p),
+                 cudaGetErrorString(e));
+        return KDL_ECUDA;
+    }
+    return KDL_OK;
+}
+
+}  // namespace dwt
+}  // namespace kdl

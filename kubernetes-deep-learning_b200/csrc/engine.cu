@@ -14,6 +14,7 @@
 
 #include "../../include/kdl.h"
 #include "gemm_tc.cuh"
+#include "dw_tma.cuh"
 #include "kernels.cuh"
 
 using namespace kdl;
@@ -101,6 +102,7 @@ struct KdlModel {
     float *w_conv1 = nullptr, *b_conv1 = nullptr;
     GemmW conv2, res[4];
     std::vector<float *> dw;      // [34] [9][C]
+    std::vector<float *> dwpad;   // [34] [ceil(C/64)][9][64] zero padded (TMA depthwise kernel)
     std::vector<GemmW> pw;        // [34]
     float *W1 = nullptr, *b1 = nullptr, *W2 = nullptr, *b2 = nullptr;
     std::vector<void *> owned;    // every device allocation (freed in destroy)
@@ -215,11 +217,18 @@ template <typename T> struct Runner {
         return KDL_OK;
     }
 
-    int dwconv(const T *in, const float *w, T *out, int H, int C, int relu_in) {
+    int dwconv(const T *in, const float *w, const float *wpad, T *out, int H, int C, int relu_in) {
         int rows = H >= 64 ? 8 : (H >= 16 ? 5 : H);
         int vec = H * (C / 4);
         dim3 grid((vec + 127) / 128, (H + rows - 1) / rows, B);
         prof_open(m, st, PC_DW, 18.0 * B * H * H * C, 2.0 * B * H * H * C * sizeof(T) + 36.0 * C);
+        if (use_tc()) {
+            int rc = dwt::launch(m->tma, (const bf16 *)in, wpad, (bf16 *)out, B, H, H, C, relu_in, st, m->err);
+            prof_close(m, st);
+            if (rc != KDL_OK) return rc;
+            m->launches++;
+            return KDL_OK;
+        }
         k_dw3x3<T><<<grid, 128, 0, st>>>(in, w, out, H, H, C, relu_in, rows);
         prof_close(m, st);
         LAUNCH_CHECK();
@@ -321,12 +330,12 @@ template <typename T> struct Runner {
             snprintf(name, sizeof name, "block%d_res_bn", blk);
             RUN(tap(name, R, Ho, rg.N, 0));
             // sepconv1: ReLU on load except block2 (input is already post-ReLU there)
-            RUN(dwconv(X, m->dw[si], Tb, H, m->pw[si].K, blk != 2));
+            RUN(dwconv(X, m->dw[si], m->dwpad[si], Tb, H, m->pw[si].K, blk != 2));
             RUN(gemm(Tb, m->pw[si], nullptr, U, B * H * H, 1, dense));  // next sepconv's ReLU folded here
             snprintf(name, sizeof name, "block%d_sepconv1_bn", blk);
             RUN(tap(name, U, H, m->pw[si].N, 1));
             ++si;
-            RUN(dwconv(U, m->dw[si], Tb, H, m->pw[si].K, 0));
+            RUN(dwconv(U, m->dw[si], m->dwpad[si], Tb, H, m->pw[si].K, 0));
             RUN(gemm(Tb, m->pw[si], nullptr, U, B * H * H, 0, dense));
             snprintf(name, sizeof name, "block%d_sepconv2_bn", blk);
             RUN(tap(name, U, H, m->pw[si].N, 0));
@@ -344,17 +353,17 @@ template <typename T> struct Runner {
         {
             const int H = sp[5], M = B * H * H;
             for (int blk = 5; blk <= 12; ++blk) {
-                RUN(dwconv(X, m->dw[si], Tb, H, 728, 1));
+                RUN(dwconv(X, m->dw[si], m->dwpad[si], Tb, H, 728, 1));
                 RUN(gemm(Tb, m->pw[si], nullptr, U, M, 1, dense));
                 snprintf(name, sizeof name, "block%d_sepconv1_bn", blk);
                 RUN(tap(name, U, H, 728, 1));
                 ++si;
-                RUN(dwconv(U, m->dw[si], Tb, H, 728, 0));
+                RUN(dwconv(U, m->dw[si], m->dwpad[si], Tb, H, 728, 0));
                 RUN(gemm(Tb, m->pw[si], nullptr, U, M, 1, dense));
                 snprintf(name, sizeof name, "block%d_sepconv2_bn", blk);
                 RUN(tap(name, U, H, 728, 1));
                 ++si;
-                RUN(dwconv(U, m->dw[si], Tb, H, 728, 0));
+                RUN(dwconv(U, m->dw[si], m->dwpad[si], Tb, H, 728, 0));
                 RUN(gemm(Tb, m->pw[si], X, X, M, 0, dense));  // + residual, in place on the skip tensor
                 ++si;
                 snprintf(name, sizeof name, "block%d_out", blk);
@@ -365,11 +374,11 @@ template <typename T> struct Runner {
         // ---- block14: ReLU after BN ----
         {
             const int H = sp[6], M = B * H * H;
-            RUN(dwconv(X, m->dw[si], Tb, H, 1024, 0));
+            RUN(dwconv(X, m->dw[si], m->dwpad[si], Tb, H, 1024, 0));
             RUN(gemm(Tb, m->pw[si], nullptr, U, M, 1, dense));
             RUN(tap("block14_sepconv1_act", U, H, 1536, 1));
             ++si;
-            RUN(dwconv(U, m->dw[si], Tb, H, 1536, 0));
+            RUN(dwconv(U, m->dw[si], m->dwpad[si], Tb, H, 1536, 0));
             RUN(gemm(Tb, m->pw[si], nullptr, U, M, 1, dense));
             RUN(tap("block14_sepconv2_act", U, H, 2048, 1));
             ++si;
@@ -493,6 +502,7 @@ extern "C" int kdl_load_weights(KdlModel *m, const float *blob, size_t n_floats)
     }
     auto seps = sep_specs();
     m->dw.assign(seps.size(), nullptr);
+    m->dwpad.assign(seps.size(), nullptr);
     m->pw.assign(seps.size(), GemmW());
     size_t si = 0;
     auto load_sep = [&](const SepSpec &s) -> int {
@@ -501,6 +511,14 @@ extern "C" int kdl_load_weights(KdlModel *m, const float *blob, size_t n_floats)
         BnFold f = fold_bn(p, s.cout);
         int r = upload(m, (void **)&m->dw[si], dwk, 9 * (size_t)s.cin * 4);
         if (r) return r;
+        {
+            int nch = (s.cin + 63) / 64;
+            std::vector<float> wp((size_t)nch * 9 * 64, 0.f);
+            for (int t = 0; t < 9; ++t)
+                for (int c = 0; c < s.cin; ++c) wp[((size_t)(c / 64) * 9 + t) * 64 + (c % 64)] = dwk[(size_t)t * s.cin + c];
+            r = upload(m, (void **)&m->dwpad[si], wp.data(), wp.size() * 4);
+            if (r) return r;
+        }
         r = make_gemm(m, m->pw[si], pwk, s.cin, s.cout, &f, nullptr);
         ++si;
         return r;
@@ -611,7 +629,7 @@ extern "C" int kdl_create(const KdlConfig *cfg, KdlModel **out) {
     CK(cudaStreamCreateWithFlags(&m->own_stream, cudaStreamNonBlocking));
     CK(cudaFuncSetAttribute(k_gap_head<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
     CK(cudaFuncSetAttribute(k_gap_head<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
-    if ((rc = tc::configure(m->err)) != KDL_OK) { set_err(g_err, "%s", m->err); kdl_destroy(m); return rc; }
+    if ((rc = tc::configure(m->err)) != KDL_OK || (rc = dwt::configure(m->err)) != KDL_OK) { set_err(g_err, "%s", m->err); kdl_destroy(m); return rc; }
     *out = m;
     return KDL_OK;
 }
