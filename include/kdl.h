@@ -125,6 +125,27 @@ int kdl_last_launch_count(const KdlModel *m);
 int kdl_gemm_bf16(const void *d_A, const void *d_Wt, const float *d_bias, const void *d_residual,
                   void *d_out, int32_t M, int32_t N, int32_t K, int32_t relu, void *stream);
 
+/* No counterpart in the reference.  kdl_preprocess_u8 for callers that cannot allocate device memory: a request thread that
+ * must stay clear of the allocator (its locks and implicit device synchronisation), a plugin living inside someone else's
+ * memory budget, or code that has no KdlModel (whose arena normally holds the index tables).  Same result as
+ * kdl_preprocess_u8, bit for bit; the per-image index tables live in one fixed device array built into the library instead
+ * of in cudaMalloc'ed buffers, and the call performs no cudaMalloc / cudaFree / allocating library call and no host->device
+ * copy (the image metadata travels as a kernel argument).
+ *   - Limits: B <= KDL_STATIC_MAX_BATCH images per call, target side S <= KDL_STATIC_MAX_SIZE; larger values are refused
+ *     with KDL_EINVAL and a message.  The array takes KDL_STATIC_SCRATCH_BYTES on every GPU that loads the library, until exit.
+ *   - Works on the CURRENT CUDA device (d_src / d_out must belong to it).  The first call on each device resolves the array's
+ *     device address (cudaGetSymbolAddress); make that first call outside any stream capture.
+ *   - All calls on a device share the array and it keeps the previous call's contents.  Nothing needs clearing (each call
+ *     rewrites every entry it reads), but two calls whose kernels overlap on the GPU (different streams, or threads racing on
+ *     one stream) corrupt each other: serialise them on one stream or with events.
+ *   - offset/h/w/pitch are HOST arrays of length B, as for kdl_preprocess_u8.  Errors: text is copied into err (may be NULL). */
+#define KDL_STATIC_MAX_BATCH 32
+#define KDL_STATIC_MAX_SIZE 512
+#define KDL_STATIC_SCRATCH_BYTES (1024 + 2 * KDL_STATIC_MAX_BATCH * KDL_STATIC_MAX_SIZE * 4)
+int kdl_preprocess_u8_static(const uint8_t *d_src, const int64_t *offset, const int32_t *h, const int32_t *w,
+                             const int64_t *pitch, int32_t B, int32_t S, float *d_out, void *stream, char *err,
+                             size_t err_len);
+
 /* Library / build info string (arch, kernels compiled in). */
 const char *kdl_version(void);
 

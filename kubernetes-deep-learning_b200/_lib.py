@@ -16,8 +16,9 @@ SYMBOLS = [
     "kdl_create", "kdl_destroy", "kdl_last_error", "kdl_weight_count", "kdl_load_weights",
     "kdl_preprocess_u8", "kdl_forward", "kdl_predict_u8", "kdl_predict_u8_host", "kdl_forward_host",
     "kdl_num_taps", "kdl_tap_name", "kdl_layer_output", "kdl_last_launch_count", "kdl_gemm_bf16",
-    "kdl_version", "kdl_profile_begin", "kdl_profile_end",
+    "kdl_version", "kdl_profile_begin", "kdl_profile_end", "kdl_preprocess_u8_static",
 ]
+STATIC_MAX_BATCH, STATIC_MAX_SIZE = 32, 512
 
 
 class KdlConfig(ctypes.Structure):
@@ -69,6 +70,7 @@ def load():
     lib.kdl_last_launch_count.argtypes = [P]
     lib.kdl_gemm_bf16.argtypes = [P, P, P, P, P, c_int32, c_int32, c_int32, c_int32, P]
     lib.kdl_version.restype = c_char_p
+    lib.kdl_preprocess_u8_static.argtypes = [P, P, P, P, P, c_int32, c_int32, P, P, c_char_p, c_size_t]
     lib.kdl_profile_begin.argtypes = [P]
     lib.kdl_profile_end.argtypes = [P, POINTER(KdlProfileRow), c_int32, POINTER(c_int32)]
     for s in SYMBOLS:
