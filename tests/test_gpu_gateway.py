@@ -81,3 +81,22 @@ def test_predict_batch_mixed_sizes(gw):
     for i, r in enumerate(res):
         got = np.array(list(r.values()))
         assert rel(got, want[i]) <= 2e-2 and got.argmax() == want[i].argmax()
+
+
+def test_replica_set_matches_single_model():
+    """In-process replicas over every visible GPU give the same logits, in input order, as one model."""
+    import kdl_b200  # noqa: F401
+    from kdl_b200 import engine, replicas, weights
+    W = weights.make_weights(1, "calibrated")
+    rng = np.random.default_rng(31)
+    imgs = [rng.integers(0, 256, (int(rng.integers(64, 600)), int(rng.integers(64, 600)), 3), dtype=np.uint8) for _ in range(7)]
+    single = engine.Model(W, max_batch=8, precision="bf16")
+    want = single.predict_uint8(imgs)
+    single.close()
+    rs = replicas.ReplicaSet(W, max_batch=8, precision="bf16")
+    try:
+        got = rs.predict_uint8(imgs)
+        assert len(rs.models) == torch.cuda.device_count()
+    finally:
+        rs.close()
+    np.testing.assert_array_equal(got, want)
