@@ -36,6 +36,33 @@ template <> struct V4<bf16> {
     }
 };
 
+// 8 consecutive channels: one 16-byte access for bf16, two for float
+template <typename T> __device__ __forceinline__ void st8(T *p, float4 a, float4 b);
+template <> __device__ __forceinline__ void st8<float>(float *p, float4 a, float4 b) {
+    *reinterpret_cast<float4 *>(p) = a;
+    *reinterpret_cast<float4 *>(p + 4) = b;
+}
+template <> __device__ __forceinline__ void st8<bf16>(bf16 *p, float4 a, float4 b) {
+    __nv_bfloat162 v0 = __floats2bfloat162_rn(a.x, a.y), v1 = __floats2bfloat162_rn(a.z, a.w);
+    __nv_bfloat162 v2 = __floats2bfloat162_rn(b.x, b.y), v3 = __floats2bfloat162_rn(b.z, b.w);
+    uint4 r;
+    r.x = *reinterpret_cast<uint32_t *>(&v0); r.y = *reinterpret_cast<uint32_t *>(&v1);
+    r.z = *reinterpret_cast<uint32_t *>(&v2); r.w = *reinterpret_cast<uint32_t *>(&v3);
+    *reinterpret_cast<uint4 *>(p) = r;
+}
+template <typename T> __device__ __forceinline__ void ld8(const T *p, float4 &a, float4 &b);
+template <> __device__ __forceinline__ void ld8<float>(const float *p, float4 &a, float4 &b) {
+    a = *reinterpret_cast<const float4 *>(p);
+    b = *reinterpret_cast<const float4 *>(p + 4);
+}
+template <> __device__ __forceinline__ void ld8<bf16>(const bf16 *p, float4 &a, float4 &b) {
+    const uint4 r = *reinterpret_cast<const uint4 *>(p);
+    a = make_float4(__uint_as_float(r.x << 16), __uint_as_float(r.x & 0xffff0000u), __uint_as_float(r.y << 16),
+                    __uint_as_float(r.y & 0xffff0000u));
+    b = make_float4(__uint_as_float(r.z << 16), __uint_as_float(r.z & 0xffff0000u), __uint_as_float(r.w << 16),
+                    __uint_as_float(r.w & 0xffff0000u));
+}
+
 template <typename T> __device__ __forceinline__ float ld1(const T *p);
 template <> __device__ __forceinline__ float ld1<float>(const float *p) { return *p; }
 template <> __device__ __forceinline__ float ld1<bf16>(const bf16 *p) { return __bfloat162float(*p); }

@@ -300,12 +300,12 @@ template <typename T> struct Runner {
         char name[64];
         // ---- block1 ----
         {
-            long long threads = (long long)B * sp[1] * sp[1] * 4;
-            unsigned grid = (unsigned)((threads + 255) / 256);
+            long long threads = (long long)B * sp[1] * sp[1];
+            unsigned grid = (unsigned)((threads + 127) / 128);
             prof_open(m, st, PC_CONV1, 2.0 * 27 * 32 * B * sp[1] * sp[1],
                       (double)B * sp[0] * sp[0] * 3 * (in_f32 ? 4 : 1) + (double)B * sp[1] * sp[1] * 32 * sizeof(T));
-            if (in_f32) k_conv1<float, T><<<grid, 256, 0, st>>>(in_f32, m->w_conv1, m->b_conv1, U, B, sp[0], sp[1]);
-            else k_conv1<uint8_t, T><<<grid, 256, 0, st>>>(in_u8, m->w_conv1, m->b_conv1, U, B, sp[0], sp[1]);
+            if (in_f32) k_conv1<float, T><<<grid, 128, 0, st>>>(in_f32, m->w_conv1, m->b_conv1, U, B, sp[0], sp[1]);
+            else k_conv1<uint8_t, T><<<grid, 128, 0, st>>>(in_u8, m->w_conv1, m->b_conv1, U, B, sp[0], sp[1]);
             prof_close(m, st);
             LAUNCH_CHECK();
             RUN(tap("block1_conv1_act", U, sp[1], 32, 1));

@@ -89,49 +89,52 @@ __global__ void k_resize(const uint8_t *__restrict__ src, const ImgMeta *__restr
 // the resized uint8 image (scaled on load with the gateway's exact arithmetic).  Memory-bound, K=27.
 // One thread = one output pixel x 8 output channels (4 threads per pixel -> 64 B contiguous per pixel).
 // ---------------------------------------------------------------------------------------------------
-template <typename TIn> __device__ __forceinline__ float in_px(const TIn *p);
-template <> __device__ __forceinline__ float in_px<float>(const float *p) { return __ldg(p); }
-template <> __device__ __forceinline__ float in_px<uint8_t>(const uint8_t *p) { return scale_px(__ldg(p)); }
+template <typename TIn> struct InPx;
+template <> struct InPx<float> {
+    static __device__ __forceinline__ float get(const float *p, const float *) { return __ldg(p); }
+};
+template <> struct InPx<uint8_t> {  // the gateway's x/127.5-1 through a 256-entry table built with the exact arithmetic
+    static __device__ __forceinline__ float get(const uint8_t *p, const float *lut) { return lut[__ldg(p)]; }
+};
 
+// One thread = one output pixel x all 32 output channels (27 inputs x 32 FMAs, weights broadcast from shared memory);
+// a warp writes 32 adjacent pixels = 2 KB contiguous.
 template <typename TIn, typename T>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(128)
 k_conv1(const TIn *__restrict__ in, const float *__restrict__ w /*[27][32]*/, const float *__restrict__ bias,
         T *__restrict__ out, int B, int S, int Ho) {
-    __shared__ float ws[27 * 32];
-    __shared__ float bs[32];
+    __shared__ __align__(16) float ws[27 * 32];
+    __shared__ __align__(16) float bs[32];
+    __shared__ float lut[256];
     for (int i = threadIdx.x; i < 27 * 32; i += blockDim.x) ws[i] = w[i];
     if (threadIdx.x < 32) bs[threadIdx.x] = bias[threadIdx.x];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) lut[i] = scale_px((uint8_t)i);
     __syncthreads();
-    long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    long long npix = (long long)B * Ho * Ho;
-    long long pix = t >> 2;
-    int cg = (int)(t & 3);
+    const long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long npix = (long long)B * Ho * Ho;
     if (pix >= npix) return;
-    int b = (int)(pix / (Ho * Ho));
-    int r = (int)(pix - (long long)b * Ho * Ho);
-    int oy = r / Ho, ox = r - oy * Ho;
+    const int b = (int)(pix / (Ho * Ho));
+    const int r = (int)(pix - (long long)b * Ho * Ho);
+    const int oy = r / Ho, ox = r - oy * Ho;
     const TIn *base = in + (((long long)b * S + 2 * oy) * S + 2 * ox) * 3;
-    float acc[8];
+    float v[27];
 #pragma unroll
-    for (int c = 0; c < 8; ++c) acc[c] = 0.f;
+    for (int ky = 0; ky < 3; ++ky)
 #pragma unroll
-    for (int ky = 0; ky < 3; ++ky) {
+        for (int kk = 0; kk < 9; ++kk) v[ky * 9 + kk] = InPx<TIn>::get(base + (long long)ky * S * 3 + kk, lut);
+    float4 acc[8];
 #pragma unroll
-        for (int kk = 0; kk < 9; ++kk) {  // kx*3+ci : 9 contiguous input values per kernel row
-            float v = in_px<TIn>(base + (long long)ky * S * 3 + kk);
-            const float4 *wp = reinterpret_cast<const float4 *>(&ws[(ky * 9 + kk) * 32 + cg * 8]);
-            float4 w0 = wp[0], w1 = wp[1];
-            acc[0] = fmaf(v, w0.x, acc[0]); acc[1] = fmaf(v, w0.y, acc[1]);
-            acc[2] = fmaf(v, w0.z, acc[2]); acc[3] = fmaf(v, w0.w, acc[3]);
-            acc[4] = fmaf(v, w1.x, acc[4]); acc[5] = fmaf(v, w1.y, acc[5]);
-            acc[6] = fmaf(v, w1.z, acc[6]); acc[7] = fmaf(v, w1.w, acc[7]);
-        }
+    for (int c = 0; c < 8; ++c) acc[c] = *reinterpret_cast<const float4 *>(&bs[c * 4]);
+#pragma unroll
+    for (int k = 0; k < 27; ++k) {
+        const float4 *wp = reinterpret_cast<const float4 *>(&ws[k * 32]);
+        const float4 a = make_float4(v[k], v[k], v[k], v[k]);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) acc[c] = fma4(a, wp[c], acc[c]);
     }
-    T *o = out + pix * 32 + cg * 8;
-    float4 a0 = make_float4(acc[0] + bs[cg * 8 + 0], acc[1] + bs[cg * 8 + 1], acc[2] + bs[cg * 8 + 2], acc[3] + bs[cg * 8 + 3]);
-    float4 a1 = make_float4(acc[4] + bs[cg * 8 + 4], acc[5] + bs[cg * 8 + 5], acc[6] + bs[cg * 8 + 6], acc[7] + bs[cg * 8 + 7]);
-    V4<T>::st(o, relu4(a0));
-    V4<T>::st(o + 4, relu4(a1));
+    T *o = out + pix * 32;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) st8<T>(o + c * 8, relu4(acc[2 * c]), relu4(acc[2 * c + 1]));
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -196,7 +199,7 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 k_maxpool_add(const T *__restrict__ in, const T *__restrict__ res, T *__restrict__ out, int B, int H, int W,
               int C, int Ho, int Wo, int pad_lo) {
-    const int CV = C >> 2;
+    const int CV = C >> 3;  // 8 channels per thread
     long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     long long total = (long long)B * Ho * Wo * CV;
     if (t >= total) return;
@@ -206,21 +209,28 @@ k_maxpool_add(const T *__restrict__ in, const T *__restrict__ res, T *__restrict
     long long q = p / Wo;
     int oy = (int)(q % Ho);
     int b = (int)(q / Ho);
-    const int c = cv << 2;
-    float4 m = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+    const int c = cv << 3;
+    const float NI = -INFINITY;
+    float4 m0 = make_float4(NI, NI, NI, NI), m1 = m0;
+    float4 v0[9], v1[9];
 #pragma unroll
     for (int dy = 0; dy < 3; ++dy) {
-        int iy = 2 * oy - pad_lo + dy;
-        if (iy < 0 || iy >= H) continue;
 #pragma unroll
         for (int dx = 0; dx < 3; ++dx) {
-            int ix = 2 * ox - pad_lo + dx;
-            if (ix < 0 || ix >= W) continue;
-            m = max4(m, V4<T>::ld(in + (((size_t)b * H + iy) * W + ix) * C + c));
+            int iy = 2 * oy - pad_lo + dy, ix = 2 * ox - pad_lo + dx;
+            bool ok = iy >= 0 && iy < H && ix >= 0 && ix < W;
+            const T *ptr = in + (((size_t)b * H + (ok ? iy : 0)) * W + (ok ? ix : 0)) * C + c;
+            v0[dy * 3 + dx] = m0;
+            v1[dy * 3 + dx] = m0;
+            if (ok) ld8<T>(ptr, v0[dy * 3 + dx], v1[dy * 3 + dx]);
         }
     }
     size_t o = (((size_t)b * Ho + oy) * Wo + ox) * C + c;
-    V4<T>::st(out + o, add4(m, V4<T>::ld(res + o)));
+    float4 r0, r1;
+    ld8<T>(res + o, r0, r1);
+#pragma unroll
+    for (int k = 0; k < 9; ++k) { m0 = max4(m0, v0[k]); m1 = max4(m1, v1[k]); }
+    st8<T>(out + o, add4(m0, r0), add4(m1, r1));
 }
 
 // Compact copy of the even-index pixels: the input of a Conv2D(1x1, strides 2, 'same') residual projection
