@@ -39,7 +39,7 @@ struct Params {
 inline Params make_params(int B, int H, int W, int C, int relu_in) {
     Params p;
     p.B = B; p.H = H; p.W = W; p.C = C; p.relu_in = relu_in;
-    int ntx = (W + 36) / 37;
+    int ntx = (W + 19) / 20;                 // tiles <= 20 columns wide: 10 column pairs x 16 channel groups = 160 threads per strip
     p.TW = (W + ntx - 1) / ntx;
     p.ntx = ntx;
     p.CP = (p.TW + 1) / 2;
@@ -51,8 +51,9 @@ inline Params make_params(int B, int H, int W, int C, int relu_in) {
     p.TH = (H + p.nty - 1) / p.nty;
     p.BH = p.TH + 2;
     int per_strip = 16 * p.CP;
-    int ns = 352 / per_strip;          // strips cost (RS+2)/RS extra row scatters: keep them >= 8 rows tall
-    if (ns > p.TH / 8) ns = p.TH / 8;
+    int ns = 480 / per_strip;                // strips only re-load their 2 halo rows (the scatter is peeled), so 3 is cheap
+    if (ns > 3) ns = 3;
+    if (ns > p.TH) ns = p.TH;
     if (ns < 1) ns = 1;
     p.RS = (p.TH + ns - 1) / ns;
     p.NS = (p.TH + p.RS - 1) / p.RS;
@@ -102,8 +103,46 @@ template <bool RELU> __device__ __forceinline__ Px ld_px(uint32_t addr) {
     return p;
 }
 
+// Scatter one staged input row (4 adjacent pixels x 4 channels of this thread) into the output rows it touches:
+// bottom taps (ky = 2) -> aA (row r-1, completes it), middle taps (ky = 1) -> aB (row r), top taps (ky = 0) -> aC (opens row r+1).
+// The first / last input rows of a strip only need part of that, hence the compile-time switches.
+template <bool RELU, bool DO_A, bool DO_B, bool DO_C>
+__device__ __forceinline__ void scatter_row(uint32_t rowaddr, const float2 (&wl)[9], const float2 (&wh)[9], float2 (&aA)[2][2],
+                                            float2 (&aB)[2][2], float2 (&aC)[2][2]) {
+    Px in[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) in[j] = ld_px<RELU>(rowaddr + 128u * j);
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+        if (DO_A) {
+#pragma unroll
+            for (int kx = 0; kx < 3; ++kx) {
+                aA[j][0] = ffma2(in[j + kx].lo, wl[6 + kx], aA[j][0]);
+                aA[j][1] = ffma2(in[j + kx].hi, wh[6 + kx], aA[j][1]);
+            }
+        }
+        if (DO_B) {
+#pragma unroll
+            for (int kx = 0; kx < 3; ++kx) {
+                aB[j][0] = ffma2(in[j + kx].lo, wl[3 + kx], aB[j][0]);
+                aB[j][1] = ffma2(in[j + kx].hi, wh[3 + kx], aB[j][1]);
+            }
+        }
+        if (DO_C) {
+            float2 cl = fmul2(in[j].lo, wl[0]), ch = fmul2(in[j].hi, wh[0]);
+#pragma unroll
+            for (int kx = 1; kx < 3; ++kx) {
+                cl = ffma2(in[j + kx].lo, wl[kx], cl);
+                ch = ffma2(in[j + kx].hi, wh[kx], ch);
+            }
+            aC[j][0] = cl;
+            aC[j][1] = ch;
+        }
+    }
+}
+
 template <bool RELU>
-__global__ void __launch_bounds__(384, 1)
+__global__ void __launch_bounds__(512, 1)
 k_dw_tma(const __grid_constant__ CUtensorMap tmIn, const float *__restrict__ wpad /*[nch][9][64]*/, bf16 *__restrict__ out, Params p) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (tc::smem_u32(smem_raw) + 127u) & ~127u;
@@ -174,53 +213,44 @@ k_dw_tma(const __grid_constant__ CUtensorMap tmIn, const float *__restrict__ wpa
                 wh[k] = make_float2(w4.z, w4.w);
             }
             const bool st1 = (2 * cp + 1 < p.TW) && (x0 + 1 < p.W);
-            // points at output row y_lo - 1 (first store happens after the first increment)
-            bf16 *o = out + (((size_t)b * p.H + (size_t)ty * p.TH + y_lo) * p.W + x0) * p.C + c - (size_t)p.W * p.C;
+            bf16 *o = out + (((size_t)b * p.H + (size_t)ty * p.TH + y_lo) * p.W + x0) * p.C + c;
             const size_t orow = (size_t)p.W * p.C;
             // accumulators of output rows (r-1, r, r+1) relative to the input row r being scattered; [col][lo/hi]
             float2 aA[2][2], aB[2][2], aC[2][2];
-            const float2 z2 = make_float2(0.f, 0.f);
-#pragma unroll
-            for (int j = 0; j < 2; ++j) { aA[j][0] = aA[j][1] = aB[j][0] = aB[j][1] = z2; }
             // staged row index = tile-relative input row + 1; thread's columns start at staged column 2*cp
             uint32_t rowaddr = tile + ((uint32_t)(y_lo * p.BW) + 2u * cp) * 128u + (uint32_t)cg * 8u;
             const uint32_t rowpitch = (uint32_t)p.BW * 128u;
-            for (int r = y_lo - 1; r <= y_hi; ++r, rowaddr += rowpitch) {
-                Px in[4];
-#pragma unroll
-                for (int j = 0; j < 4; ++j) in[j] = ld_px<RELU>(rowaddr + 128u * j);
-#pragma unroll
-                for (int j = 0; j < 2; ++j) {
-                    // bottom taps (ky = 2) complete output row r-1; middle taps (ky = 1) -> row r; top taps start row r+1
-                    float2 cl = fmul2(in[j].lo, wl[0]), chh = fmul2(in[j].hi, wh[0]);
-#pragma unroll
-                    for (int kx = 0; kx < 3; ++kx) {
-                        aA[j][0] = ffma2(in[j + kx].lo, wl[6 + kx], aA[j][0]);
-                        aA[j][1] = ffma2(in[j + kx].hi, wh[6 + kx], aA[j][1]);
-                        aB[j][0] = ffma2(in[j + kx].lo, wl[3 + kx], aB[j][0]);
-                        aB[j][1] = ffma2(in[j + kx].hi, wh[3 + kx], aB[j][1]);
-                        if (kx > 0) {
-                            cl = ffma2(in[j + kx].lo, wl[kx], cl);
-                            chh = ffma2(in[j + kx].hi, wh[kx], chh);
-                        }
-                    }
-                    aC[j][0] = cl;
-                    aC[j][1] = chh;
-                }
-                if (r > y_lo) {  // output row r-1 is complete
-                    uint2 v0, v1;
-                    v0.x = tc::pack_bf16(aA[0][0].x, aA[0][0].y); v0.y = tc::pack_bf16(aA[0][1].x, aA[0][1].y);
-                    v1.x = tc::pack_bf16(aA[1][0].x, aA[1][0].y); v1.y = tc::pack_bf16(aA[1][1].x, aA[1][1].y);
-                    *reinterpret_cast<uint2 *>(o) = v0;
-                    if (st1) *reinterpret_cast<uint2 *>(o + p.C) = v1;
-                }
-                if (r >= y_lo) o += orow;
+            auto store_row = [&]() {  // output row held in aA is complete
+                uint2 v0, v1;
+                v0.x = tc::pack_bf16(aA[0][0].x, aA[0][0].y); v0.y = tc::pack_bf16(aA[0][1].x, aA[0][1].y);
+                v1.x = tc::pack_bf16(aA[1][0].x, aA[1][0].y); v1.y = tc::pack_bf16(aA[1][1].x, aA[1][1].y);
+                *reinterpret_cast<uint2 *>(o) = v0;
+                if (st1) *reinterpret_cast<uint2 *>(o + p.C) = v1;
+                o += orow;
+            };
+            auto rotate = [&]() {
 #pragma unroll
                 for (int j = 0; j < 2; ++j) {
                     aA[j][0] = aB[j][0]; aA[j][1] = aB[j][1];
                     aB[j][0] = aC[j][0]; aB[j][1] = aC[j][1];
                 }
+            };
+            // input row y_lo-1: only its top taps matter (they open output row y_lo)
+            scatter_row<RELU, false, false, true>(rowaddr, wl, wh, aA, aB, aC);
+            rotate();
+            rowaddr += rowpitch;
+            // input row y_lo: middle taps of row y_lo, top taps of row y_lo+1
+            scatter_row<RELU, false, true, true>(rowaddr, wl, wh, aA, aB, aC);
+            rotate();
+            rowaddr += rowpitch;
+            for (int r = y_lo + 1; r < y_hi; ++r, rowaddr += rowpitch) {
+                scatter_row<RELU, true, true, true>(rowaddr, wl, wh, aA, aB, aC);
+                store_row();
+                rotate();
             }
+            // input row y_hi: only its bottom taps matter (they close output row y_hi-1)
+            scatter_row<RELU, true, false, false>(rowaddr, wl, wh, aA, aB, aC);
+            store_row();
         }
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(empty_bar(stage));

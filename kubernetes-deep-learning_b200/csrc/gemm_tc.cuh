@@ -36,14 +36,15 @@ constexpr int BLOCK_K = 64;   // standard configuration: 64 bf16 = 128 bytes = o
 template <int SW, int BN, bool CONV> struct Cfg {
     static constexpr int BLOCK_N = BN;
     static constexpr int BLOCK_K = SW / 2;  // elements per k-block = one swizzle row
-    static constexpr int STAGES = CONV ? 8 : 4;
+    static constexpr int STAGES = CONV ? 12 : 4;
     static constexpr uint32_t A_BYTES = BLOCK_M * SW;
-    static constexpr uint32_t B_BYTES = BN * SW;
+    static constexpr uint32_t B_BYTES = CONV ? 0 : BN * SW;           // conv mode keeps all 9 weight taps resident instead
+    static constexpr uint32_t W_RES_BYTES = CONV ? 9 * BN * SW : 0;   // 9 taps x [64 out-ch x 32 in-ch] bf16 = 36 KB
     static constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr uint32_t EPI_BYTES = CONV ? 0 : 4 * 2 * 4096;  // per epilogue warp: 2 x (32 rows x 128 B)
     static constexpr uint32_t BIAS_BYTES = BN * 4;
     static constexpr uint32_t BAR_BYTES = 256;
-    static constexpr uint32_t SMEM_BYTES = STAGES * STAGE_BYTES + EPI_BYTES + BIAS_BYTES + BAR_BYTES + 1024 /*align slack*/;
+    static constexpr uint32_t SMEM_BYTES = STAGES * STAGE_BYTES + W_RES_BYTES + EPI_BYTES + BIAS_BYTES + BAR_BYTES + 1024 /*align slack*/;
     static constexpr uint32_t TMEM_COLS = 2 * BN <= 32 ? 32 : 2 * BN <= 64 ? 64 : 2 * BN <= 128 ? 128 : 2 * BN <= 256 ? 256 : 512;
     static_assert(SMEM_BYTES <= 232448, "exceeds 227 KB of shared memory per CTA");
     static_assert(2 * BN <= 512, "two accumulators must fit the 512 TMEM columns");
@@ -264,7 +265,8 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     constexpr int BK = C::BLOCK_K;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // swizzled tiles need 1024-byte alignment
-    const uint32_t epi_base = smem_base + STAGES * C::STAGE_BYTES;
+    const uint32_t wres_base = smem_base + STAGES * C::STAGE_BYTES;  // conv mode: resident weight taps
+    const uint32_t epi_base = wres_base + C::W_RES_BYTES;
     const uint32_t bias_base = epi_base + C::EPI_BYTES;
     const uint32_t bar_base = bias_base + C::BIAS_BYTES;
     // barrier slots (8 B each): full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2]; then the TMEM base address
@@ -273,6 +275,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
     auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + 2 + a); };
     const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4);
+    const uint32_t wres_bar = bar_base + 8u * (2 * STAGES + 5);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -287,6 +290,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         if (!CONV) prefetch_tmap(&tmOut);
         for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
         for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4); }
+        mbar_init(wres_bar, 1);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(tmem_slot, C::TMEM_COLS);
@@ -301,6 +305,10 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
+            if (CONV) {  // all 9 weight taps once per CTA (persistent over its tiles)
+                mbar_expect_tx(wres_bar, C::W_RES_BYTES);
+                for (int t = 0; t < 9; ++t) tma_load_2d(wres_base + t * (BN * SW), &tmB, wres_bar, t * BK, 0);
+            }
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
                 const int m0 = (tile / n_tiles) * BLOCK_M, n0 = (tile % n_tiles) * BN;
                 for (int kb = 0; kb < k_blocks; ++kb) {
@@ -313,7 +321,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
                     } else {
                         tma_load_2d(sa, &tmA, full_bar(stage), kb * BK, m0);
                     }
-                    tma_load_2d(sa + C::A_BYTES, &tmB, full_bar(stage), kb * BK, n0);
+                    if (!CONV) tma_load_2d(sa + C::A_BYTES, &tmB, full_bar(stage), kb * BK, n0);
                     if (++stage == STAGES) { stage = 0; phase ^= 1u; }
                 }
             }
@@ -324,6 +332,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
+            if (CONV) mbar_wait(wres_bar, 0);
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
                 const int n0 = (tile % n_tiles) * BN;
                 const int acc = it & 1;
@@ -339,7 +348,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
                     tc_fence_after();
                     const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
                     const uint64_t adesc = make_smem_desc<SW>(sa);
-                    const uint64_t bdesc = make_smem_desc<SW>(sa + C::A_BYTES);
+                    const uint64_t bdesc = make_smem_desc<SW>(CONV ? wres_base + kb * (BN * SW) : sa + C::A_BYTES);
                     const int k_left = K - kb * BK;
                     const int ksteps = k_left >= BK ? BK / UMMA_K : (k_left + UMMA_K - 1) / UMMA_K;
                     for (int k = 0; k < ksteps; ++k) {
