@@ -7,6 +7,7 @@
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <string>
@@ -14,6 +15,7 @@
 
 #include "../../include/kdl.h"
 #include "gemm_tc.cuh"
+#include "gemm_tc2.cuh"
 #include "dw_tma.cuh"
 #include "kernels.cuh"
 
@@ -78,7 +80,8 @@ struct GemmW {
     void *Wkn = nullptr;   // storage T, [K][N]  (CUDA-core GEMM)
     bf16 *Wnk = nullptr;   // bf16, [N][K]       (tcgen05 GEMM, K-major B operand)
     float *bias = nullptr; // folded BN shift
-    CUtensorMap tmB;       // TMA descriptor of Wnk
+    CUtensorMap tmB;       // TMA descriptor of Wnk (box 64 x 256: single-CTA kernel)
+    CUtensorMap tmB2;      // TMA descriptor of Wnk (box 64 x 128: each CTA of a pair loads half of the N tile)
 };
 
 struct Tap {
@@ -93,6 +96,7 @@ struct KdlModel {
     KdlConfig cfg;
     char err[512];
     bool weights_loaded = false;
+    bool force_1cta = false;  // KDL_GEMM_1CTA=1: single-CTA tcgen05 kernel everywhere (A/B measurements)
     int launches = 0;
     int last_B = 0;
     int sp[7];  // spatial chain S,H1..H6
@@ -245,7 +249,12 @@ template <typename T> struct Runner {
         const double bytes = ((double)M * g.K + (double)M * g.N * (resid ? 2 : 1) + (double)g.K * g.N) * sizeof(T) + 4.0 * g.N;
         if (use_tc() && rm.mode == 0 && tc::shape_supported(M, g.N, g.K)) {
             prof_open(m, st, g.K >= 512 ? PC_PW_TC_TENSOR : PC_PW_TC_HBM, flops, bytes);
-            int rc = tc::launch_gemm(m->tma, (const bf16 *)A, &g.tmB, g.bias, (const bf16 *)resid, (bf16 *)out,
+            int rc;
+            if (M >= 2048 && g.K >= 512 && !m->force_1cta)  // CTA pairs pay off on the tensor-bound layers only
+                rc = tc2::launch_gemm2(m->tma, (const bf16 *)A, &g.tmB2, g.bias, (const bf16 *)resid, (bf16 *)out, M, g.N, g.K, relu,
+                                       st, m->err);
+            else
+                rc = tc::launch_gemm(m->tma, (const bf16 *)A, &g.tmB, g.bias, (const bf16 *)resid, (bf16 *)out,
                                      M, g.N, g.K, relu, st, m->err);
             prof_close(m, st);
             if (rc != KDL_OK) return rc;
@@ -466,6 +475,7 @@ static int make_gemm(KdlModel *m, GemmW &g, const float *kern, int K, int N, con
     if (m->tma.ok()) {
         bool ok = conv3x3 ? m->tma.encode_2d(&g.tmB, g.Wnk, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, 32, 64, 64)
                           : m->tma.encode_2d(&g.tmB, g.Wnk, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, tc::BLOCK_K, tc::BLOCK_N, 128);
+        if (ok && !conv3x3) ok = m->tma.encode_2d(&g.tmB2, g.Wnk, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, tc2::BK2, 128, 128);
         if (!ok) {
             set_err(m->err, "cuTensorMapEncodeTiled failed for weight [%d,%d]", N, K);
             return KDL_ECUDA;
@@ -629,7 +639,8 @@ extern "C" int kdl_create(const KdlConfig *cfg, KdlModel **out) {
     CK(cudaStreamCreateWithFlags(&m->own_stream, cudaStreamNonBlocking));
     CK(cudaFuncSetAttribute(k_gap_head<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
     CK(cudaFuncSetAttribute(k_gap_head<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
-    if ((rc = tc::configure(m->err)) != KDL_OK || (rc = dwt::configure(m->err)) != KDL_OK) { set_err(g_err, "%s", m->err); kdl_destroy(m); return rc; }
+    { const char *e1 = getenv("KDL_GEMM_1CTA"); m->force_1cta = e1 && e1[0] == '1'; }
+    if ((rc = tc::configure(m->err)) != KDL_OK || (rc = tc2::configure2(m->err)) != KDL_OK || (rc = dwt::configure(m->err)) != KDL_OK) { set_err(g_err, "%s", m->err); kdl_destroy(m); return rc; }
     *out = m;
     return KDL_OK;
 }
@@ -838,14 +849,19 @@ extern "C" int kdl_gemm_bf16(const void *d_A, const void *d_Wt, const float *d_b
     if (!enc.ok()) { set_err(g_err, "kdl_gemm_bf16: cuTensorMapEncodeTiled unavailable"); return KDL_ECUDA; }
     int rc = tc::configure(g_err);
     if (rc) return rc;
+    if ((rc = tc2::configure2(g_err))) return rc;
+    const bool one_cta = ((relu >> 1) & 1) || M < 256;
     CUtensorMap tmB;
-    if (!enc.encode_2d(&tmB, d_Wt, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, tc::BLOCK_K, tc::BLOCK_N, 128)) {
+    if (!enc.encode_2d(&tmB, d_Wt, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, tc::BLOCK_K, one_cta ? tc::BLOCK_N : 128, 128)) {
         set_err(g_err, "kdl_gemm_bf16: tensor map encode failed");
         return KDL_ECUDA;
     }
     (void)err;
-    return tc::launch_gemm(enc, (const bf16 *)d_A, &tmB, d_bias, (const bf16 *)d_residual, (bf16 *)d_out, M, N, K, relu,
-                           (cudaStream_t)stream, g_err);
+    if (one_cta)
+        return tc::launch_gemm(enc, (const bf16 *)d_A, &tmB, d_bias, (const bf16 *)d_residual, (bf16 *)d_out, M, N, K, relu & 1,
+                               (cudaStream_t)stream, g_err);
+    return tc2::launch_gemm2(enc, (const bf16 *)d_A, &tmB, d_bias, (const bf16 *)d_residual, (bf16 *)d_out, M, N, K, relu & 1,
+                             (cudaStream_t)stream, g_err);
 }
 
 // ---------------------------------------------------------------------------------------------------

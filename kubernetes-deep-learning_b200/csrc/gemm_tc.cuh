@@ -367,18 +367,40 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         const int et = threadIdx.x - 64;  // 0..127
         const uint32_t ebuf = epi_base + (uint32_t)(warp - 2) * 8192u;
         const bool has_res = residual != nullptr;
+        int staged_n0 = -1, pref_n0 = -1;
+        float bpre[(BN + 127) / 128];
         int it = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
             const int m0 = (tile / n_tiles) * BLOCK_M, n0 = (tile % n_tiles) * BN;
             const int acc = it & 1;
             const uint32_t acc_phase = (it >> 1) & 1;
-            // stage this tile's bias slice once (all four epilogue warps share it)
-            named_bar_sync(1, 128);
-            for (int j = et; j < BN; j += 128) {
-                float b = (n0 + j < N) ? __ldg(bias + n0 + j) : 0.f;
-                asm volatile("st.shared.f32 [%0], %1;" ::"r"(bias_base + 4u * j), "f"(b) : "memory");
+            // stage this tile's bias slice (all four epilogue warps share it); skipped while the N tile does not change, and the
+            // values were prefetched into registers during the previous tile so no global-load latency sits between the barriers
+            if (n0 != staged_n0) {
+                named_bar_sync(1, 128);
+                if (n0 != pref_n0) {
+#pragma unroll
+                    for (int j = 0; j < (BN + 127) / 128; ++j)
+                        bpre[j] = (et + 128 * j < BN && n0 + et + 128 * j < N) ? __ldg(bias + n0 + et + 128 * j) : 0.f;
+                }
+#pragma unroll
+                for (int j = 0; j < (BN + 127) / 128; ++j)
+                    if (et + 128 * j < BN) asm volatile("st.shared.f32 [%0], %1;" ::"r"(bias_base + 4u * (et + 128 * j)), "f"(bpre[j]) : "memory");
+                named_bar_sync(1, 128);
+                staged_n0 = n0;
             }
-            named_bar_sync(1, 128);
+            {
+                const int next = tile + gridDim.x;
+                if (next < num_tiles) {
+                    const int nn0 = (next % n_tiles) * BN;
+                    if (nn0 != staged_n0) {
+#pragma unroll
+                        for (int j = 0; j < (BN + 127) / 128; ++j)
+                            bpre[j] = (et + 128 * j < BN && nn0 + et + 128 * j < N) ? __ldg(bias + nn0 + et + 128 * j) : 0.f;
+                        pref_n0 = nn0;
+                    }
+                }
+            }
             const int row0 = m0 + q * 32;
             const int row = row0 + lane;
             const uint32_t t_row = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
