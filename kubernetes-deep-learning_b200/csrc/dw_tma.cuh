@@ -25,6 +25,7 @@ constexpr uint32_t TILE_BUDGET = 61440;      // max bytes of one staged input ti
 
 struct Params {
     int B, H, W, C;
+    int ld;          // pixel pitch in elements (>= C); 728-channel tensors use 768 so every 64-channel TMA row is 128-byte aligned
     int TW, TH;      // output tile (pixels)
     int BW;          // staged box width  = 2*CP + 2  (>= TW + 2)
     int BH;          // staged box height = TH + 2
@@ -36,9 +37,9 @@ struct Params {
     int consumer_threads;
 };
 
-inline Params make_params(int B, int H, int W, int C, int relu_in) {
+inline Params make_params(int B, int H, int W, int C, int ld, int relu_in) {
     Params p;
-    p.B = B; p.H = H; p.W = W; p.C = C; p.relu_in = relu_in;
+    p.B = B; p.H = H; p.W = W; p.C = C; p.ld = ld; p.relu_in = relu_in;
     int ntx = (W + 19) / 20;                 // tiles <= 20 columns wide: 10 column pairs x 16 channel groups = 160 threads per strip
     p.TW = (W + ntx - 1) / ntx;
     p.ntx = ntx;
@@ -213,8 +214,8 @@ k_dw_tma(const __grid_constant__ CUtensorMap tmIn, const float *__restrict__ wpa
                 wh[k] = make_float2(w4.z, w4.w);
             }
             const bool st1 = (2 * cp + 1 < p.TW) && (x0 + 1 < p.W);
-            bf16 *o = out + (((size_t)b * p.H + (size_t)ty * p.TH + y_lo) * p.W + x0) * p.C + c;
-            const size_t orow = (size_t)p.W * p.C;
+            bf16 *o = out + (((size_t)b * p.H + (size_t)ty * p.TH + y_lo) * p.W + x0) * p.ld + c;
+            const size_t orow = (size_t)p.W * p.ld;
             // accumulators of output rows (r-1, r, r+1) relative to the input row r being scattered; [col][lo/hi]
             float2 aA[2][2], aB[2][2], aC[2][2];
             // staged row index = tile-relative input row + 1; thread's columns start at staged column 2*cp
@@ -225,7 +226,7 @@ k_dw_tma(const __grid_constant__ CUtensorMap tmIn, const float *__restrict__ wpa
                 v0.x = tc::pack_bf16(aA[0][0].x, aA[0][0].y); v0.y = tc::pack_bf16(aA[0][1].x, aA[0][1].y);
                 v1.x = tc::pack_bf16(aA[1][0].x, aA[1][0].y); v1.y = tc::pack_bf16(aA[1][1].x, aA[1][1].y);
                 *reinterpret_cast<uint2 *>(o) = v0;
-                if (st1) *reinterpret_cast<uint2 *>(o + p.C) = v1;
+                if (st1) *reinterpret_cast<uint2 *>(o + p.ld) = v1;
                 o += orow;
             };
             auto rotate = [&]() {
@@ -263,7 +264,7 @@ typedef tc::EncodeTiledFn EncodeFn;
 
 inline bool encode_input_map(const tc::TmaEncoder &enc, CUtensorMap *tm, const void *in, const Params &p) {
     cuuint64_t dims[4] = {(cuuint64_t)p.C, (cuuint64_t)p.W, (cuuint64_t)p.H, (cuuint64_t)p.B};
-    cuuint64_t strides[3] = {(cuuint64_t)p.C * 2, (cuuint64_t)p.W * p.C * 2, (cuuint64_t)p.H * p.W * p.C * 2};
+    cuuint64_t strides[3] = {(cuuint64_t)p.ld * 2, (cuuint64_t)p.W * p.ld * 2, (cuuint64_t)p.H * p.W * p.ld * 2};
     cuuint32_t box[4] = {(cuuint32_t)CB, (cuuint32_t)p.BW, (cuuint32_t)p.BH, 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
     return enc.fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void *>(in), dims, strides, box, estr,
@@ -282,9 +283,9 @@ inline int configure(char *err) {
     return KDL_OK;
 }
 
-inline int launch(const tc::TmaEncoder &enc, const bf16 *in, const float *wpad, bf16 *out, int B, int H, int W, int C, int relu_in,
-                  cudaStream_t st, char *err) {
-    Params p = make_params(B, H, W, C, relu_in);
+inline int launch(const tc::TmaEncoder &enc, const bf16 *in, const float *wpad, bf16 *out, int B, int H, int W, int C, int ld,
+                  int relu_in, cudaStream_t st, char *err) {
+    Params p = make_params(B, H, W, C, ld, relu_in);
     CUtensorMap tm;
     if (!encode_input_map(enc, &tm, in, p)) {
         snprintf(err, 512, "cuTensorMapEncodeTiled(4d) failed for depthwise input [%d,%d,%d,%d] box [%d,%d]", B, H, W, C, p.BW, p.BH);

@@ -16,6 +16,7 @@
 #include "../../include/kdl.h"
 #include "gemm_tc.cuh"
 #include "gemm_tc2.cuh"
+#include "conv_tc.cuh"
 #include "dw_tma.cuh"
 #include "kernels.cuh"
 
@@ -96,7 +97,8 @@ struct KdlModel {
     KdlConfig cfg;
     char err[512];
     bool weights_loaded = false;
-    bool force_1cta = false;  // KDL_GEMM_1CTA=1: single-CTA tcgen05 kernel everywhere (A/B measurements)
+    bool conv_shifted_taps = false;  // KDL_CONV2_TAPS=1: 9 shifted TMA boxes per tile instead of the staged halo (A/B)
+    bool use_2cta = false;    // KDL_GEMM_2CTA=1: CTA-pair (cta_group::2) kernel for the K>=512 layers (A/B measurements)
     int launches = 0;
     int last_B = 0;
     int sp[7];  // spatial chain S,H1..H6
@@ -132,7 +134,7 @@ struct KdlModel {
 
     // per-launch CUDA-event profiling (kdl_profile_begin / kdl_profile_end)
     bool profiling = false;
-    struct ProfRec { int cls; cudaEvent_t a, b; };
+    struct ProfRec { int cls; cudaEvent_t a, b; double flops, bytes; char label[40]; };
     std::vector<ProfRec> prof_recs;
     std::vector<cudaEvent_t> ev_pool;
     size_t ev_used = 0;
@@ -152,9 +154,11 @@ static cudaEvent_t prof_event(KdlModel *m) {
     }
     return m->ev_pool[m->ev_used++];
 }
-static void prof_open(KdlModel *m, cudaStream_t st, int cls, double flops, double bytes) {
+static void prof_open(KdlModel *m, cudaStream_t st, int cls, double flops, double bytes, const char *fmt = nullptr, int a0 = 0,
+                      int a1 = 0, int a2 = 0) {
     if (!m->profiling) return;
-    KdlModel::ProfRec r{cls, prof_event(m), prof_event(m)};
+    KdlModel::ProfRec r{cls, prof_event(m), prof_event(m), flops, bytes, {0}};
+    if (fmt) snprintf(r.label, sizeof r.label, fmt, a0, a1, a2);
     cudaEventRecord(r.a, st);
     m->prof_recs.push_back(r);
     m->cls_flops[cls] += flops; m->cls_bytes[cls] += bytes; m->cls_launches[cls]++;
@@ -216,8 +220,10 @@ template <typename T> struct Runner {
         int i;
         int rc = alloc_tap(name, H, C, relu_applied, is_float, &i);
         if (rc) return rc;
-        size_t bytes = (size_t)B * H * H * C * (is_float ? 4 : sizeof(T));
-        CK(cudaMemcpyAsync(m->taps[i].buf, src, bytes, cudaMemcpyDeviceToDevice, st));
+        const size_t esz = is_float ? 4 : sizeof(T);
+        const size_t pitch = (is_float ? (size_t)C : (size_t)ld(C)) * esz;   // taps are stored dense
+        CK(cudaMemcpy2DAsync(m->taps[i].buf, (size_t)C * esz, src, pitch, (size_t)C * esz, (size_t)B * H * H,
+                             cudaMemcpyDeviceToDevice, st));
         return KDL_OK;
     }
 
@@ -225,9 +231,9 @@ template <typename T> struct Runner {
         int rows = H >= 64 ? 8 : (H >= 16 ? 5 : H);
         int vec = H * (C / 4);
         dim3 grid((vec + 127) / 128, (H + rows - 1) / rows, B);
-        prof_open(m, st, PC_DW, 18.0 * B * H * H * C, 2.0 * B * H * H * C * sizeof(T) + 36.0 * C);
+        prof_open(m, st, PC_DW, 18.0 * B * H * H * C, 2.0 * B * H * H * C * sizeof(T) + 36.0 * C, "dw H=%d C=%d relu=%d", H, C, relu_in);
         if (use_tc()) {
-            int rc = dwt::launch(m->tma, (const bf16 *)in, wpad, (bf16 *)out, B, H, H, C, relu_in, st, m->err);
+            int rc = dwt::launch(m->tma, (const bf16 *)in, wpad, (bf16 *)out, B, H, H, C, ld(C), relu_in, st, m->err);
             prof_close(m, st);
             if (rc != KDL_OK) return rc;
             m->launches++;
@@ -242,20 +248,25 @@ template <typename T> struct Runner {
     bool use_tc() const {
         return sizeof(T) == 2 && m->cfg.gemm_impl == KDL_GEMM_AUTO;
     }
+    // Pixel pitch (elements) of a C-channel activation tensor.  The tensor-core path pads it to a multiple of 64 so that every
+    // 64-channel TMA row starts 128-byte aligned: with C = 728 (1456-byte rows) each row straddles two L2 lines, which doubled
+    // the L2 request count and cost the K = 728 GEMMs ~35 % (measured: 716 -> 1116 TFLOP/s at pitch 768).  Only the pitch
+    // changes -- the pad lanes are never read (TMA boxes stop at C) nor written.
+    int ld(int C) const { return (use_tc() && C > 64) ? ((C + 63) / 64) * 64 : C; }
 
     // out[M,N] = act(A*W + bias) (+res).  A rows through RowMap (mode 0 = dense).
     int gemm(const T *A, const GemmW &g, const T *resid, T *out, int M, int relu, RowMap rm) {
         const double flops = 2.0 * M * g.N * g.K;
         const double bytes = ((double)M * g.K + (double)M * g.N * (resid ? 2 : 1) + (double)g.K * g.N) * sizeof(T) + 4.0 * g.N;
         if (use_tc() && rm.mode == 0 && tc::shape_supported(M, g.N, g.K)) {
-            prof_open(m, st, g.K >= 512 ? PC_PW_TC_TENSOR : PC_PW_TC_HBM, flops, bytes);
+            prof_open(m, st, g.K >= 512 ? PC_PW_TC_TENSOR : PC_PW_TC_HBM, flops, bytes, "gemm M=%d N=%d K=%d", M, g.N, g.K);
             int rc;
-            if (M >= 2048 && g.K >= 512 && !m->force_1cta)  // CTA pairs pay off on the tensor-bound layers only
+            if (m->use_2cta && M >= 2048 && g.K >= 512)  // opt-in (KDL_GEMM_2CTA=1): with 128-byte aligned rows the single-CTA kernel is faster
                 rc = tc2::launch_gemm2(m->tma, (const bf16 *)A, &g.tmB2, g.bias, (const bf16 *)resid, (bf16 *)out, M, g.N, g.K, relu,
-                                       st, m->err);
+                                       st, m->err, ld(g.K), ld(g.N));
             else
                 rc = tc::launch_gemm(m->tma, (const bf16 *)A, &g.tmB, g.bias, (const bf16 *)resid, (bf16 *)out,
-                                     M, g.N, g.K, relu, st, m->err);
+                                     M, g.N, g.K, relu, st, m->err, ld(g.K), ld(g.N));
             prof_close(m, st);
             if (rc != KDL_OK) return rc;
             m->launches++;
@@ -275,7 +286,7 @@ template <typename T> struct Runner {
         if (use_tc() && tc::shape_supported(M, g.N, g.K)) {
             long long total = (long long)M * (g.K / 4);
             prof_open(m, st, PC_SUBSAMPLE, 0.0, 2.0 * M * g.K * sizeof(T));
-            k_subsample2<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(in, (T *)m->S, B, H, H, g.K, Ho, Ho);
+            k_subsample2<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(in, (T *)m->S, B, H, H, g.K, ld(g.K), Ho, Ho);
             prof_close(m, st);
             LAUNCH_CHECK();
             return gemm((const T *)m->S, g, nullptr, out, M, 0, RowMap{0, 0, 0, 0, 0, 0});
@@ -288,8 +299,8 @@ template <typename T> struct Runner {
         if (pad_total < 0) pad_total = 0;
         int pad_lo = pad_total / 2;  // TF SAME: extra padding goes to the end
         long long total = (long long)B * Ho * Ho * (C / 4);
-        prof_open(m, st, PC_POOL, 0.0, ((double)B * H * H * C + 2.0 * B * Ho * Ho * C) * sizeof(T));
-        k_maxpool_add<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(in, resid, out, B, H, H, C, Ho, Ho, pad_lo);
+        prof_open(m, st, PC_POOL, 0.0, ((double)B * H * H * C + 2.0 * B * Ho * Ho * C) * sizeof(T), "pool H=%d C=%d", H, C);
+        k_maxpool_add<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(in, resid, out, B, H, H, C, ld(C), Ho, Ho, pad_lo);
         prof_close(m, st);
         LAUNCH_CHECK();
         return KDL_OK;
@@ -322,7 +333,9 @@ template <typename T> struct Runner {
             if (use_tc()) {
                 prof_open(m, st, PC_CONV2, 2.0 * B * sp[2] * sp[2] * 288.0 * 64.0,
                           ((double)B * sp[1] * sp[1] * 32 + (double)B * sp[2] * sp[2] * 64 + 288.0 * 64) * 2.0);
-                int rc = tc::launch_conv3x3(m->tma, (const bf16 *)U, &m->conv2.tmB, m->conv2.bias, (bf16 *)X, B, sp[1], sp[1], 1, st, m->err);
+                int rc = (convtc::geometry_supported(sp[1]) && !m->conv_shifted_taps)
+                             ? convtc::launch(m->tma, (const bf16 *)U, &m->conv2.tmB, m->conv2.bias, (bf16 *)X, B, sp[1], sp[1], 1, st, m->err)
+                             : tc::launch_conv3x3(m->tma, (const bf16 *)U, &m->conv2.tmB, m->conv2.bias, (bf16 *)X, B, sp[1], sp[1], 1, st, m->err);
                 prof_close(m, st);
                 if (rc != KDL_OK) return rc;
                 m->launches++;
@@ -461,21 +474,22 @@ static int make_gemm(KdlModel *m, GemmW &g, const float *kern, int K, int N, con
     if (m->cfg.precision == KDL_PRECISION_F32) {
         return upload(m, &g.Wkn, w.data(), w.size() * sizeof(float));
     }
-    std::vector<uint16_t> wkn((size_t)K * N), wnk((size_t)K * N);
+    const int Kp = ((K + 63) / 64) * 64;  // K-major rows padded to a 128-byte multiple (aligned TMA rows); pad is never read
+    std::vector<uint16_t> wkn((size_t)K * N), wnk((size_t)Kp * N, 0);
     for (int k = 0; k < K; ++k)
         for (int n = 0; n < N; ++n) {
             uint16_t v = f2bf(w[(size_t)k * N + n]);
             wkn[(size_t)k * N + n] = v;
-            wnk[(size_t)n * K + k] = v;
+            wnk[(size_t)n * Kp + k] = v;
         }
     rc = upload(m, &g.Wkn, wkn.data(), wkn.size() * 2);
     if (rc) return rc;
     rc = upload(m, (void **)&g.Wnk, wnk.data(), wnk.size() * 2);
     if (rc) return rc;
     if (m->tma.ok()) {
-        bool ok = conv3x3 ? m->tma.encode_2d(&g.tmB, g.Wnk, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, 32, 64, 64)
-                          : m->tma.encode_2d(&g.tmB, g.Wnk, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, tc::BLOCK_K, tc::BLOCK_N, 128);
-        if (ok && !conv3x3) ok = m->tma.encode_2d(&g.tmB2, g.Wnk, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, tc2::BK2, 128, 128);
+        bool ok = conv3x3 ? m->tma.encode_2d(&g.tmB, g.Wnk, (uint64_t)K, (uint64_t)N, (uint64_t)Kp * 2, 32, 64, 64)
+                          : m->tma.encode_2d(&g.tmB, g.Wnk, (uint64_t)K, (uint64_t)N, (uint64_t)Kp * 2, tc::BLOCK_K, tc::BLOCK_N, 128);
+        if (ok && !conv3x3) ok = m->tma.encode_2d(&g.tmB2, g.Wnk, (uint64_t)K, (uint64_t)N, (uint64_t)Kp * 2, tc2::BK2, 128, 128);
         if (!ok) {
             set_err(m->err, "cuTensorMapEncodeTiled failed for weight [%d,%d]", N, K);
             return KDL_ECUDA;
@@ -610,13 +624,13 @@ extern "C" int kdl_create(const KdlConfig *cfg, KdlModel **out) {
     const size_t MB = cfg->max_batch;
     auto sq = [](int h) { return (size_t)h * h; };
     size_t maxel = 0;
-    size_t cands[] = {sq(sp[1]) * 32, sq(sp[2]) * 128, sq(sp[3]) * 256, sq(sp[4]) * 728, sq(sp[5]) * 1024, sq(sp[6]) * 2048};
+    size_t cands[] = {sq(sp[1]) * 32, sq(sp[2]) * 128, sq(sp[3]) * 256, sq(sp[4]) * 768, sq(sp[5]) * 1024, sq(sp[6]) * 2048};
     for (size_t c : cands) maxel = c > maxel ? c : maxel;
     size_t rel = 0;
-    size_t rc_[] = {sq(sp[3]) * 128, sq(sp[4]) * 256, sq(sp[5]) * 728, sq(sp[6]) * 1024};
+    size_t rc_[] = {sq(sp[3]) * 128, sq(sp[4]) * 256, sq(sp[5]) * 768, sq(sp[6]) * 1024};
     for (size_t c : rc_) rel = c > rel ? c : rel;
     size_t sel = 0;
-    size_t sc_[] = {sq(sp[3]) * 64, sq(sp[4]) * 128, sq(sp[5]) * 256, sq(sp[6]) * 728};
+    size_t sc_[] = {sq(sp[3]) * 64, sq(sp[4]) * 128, sq(sp[5]) * 256, sq(sp[6]) * 768};
     for (size_t c : sc_) sel = c > sel ? c : sel;
     int rc = KDL_OK;
     // +tile slack: TMA boxes of the last M tile may read past M rows (results are discarded)
@@ -639,8 +653,9 @@ extern "C" int kdl_create(const KdlConfig *cfg, KdlModel **out) {
     CK(cudaStreamCreateWithFlags(&m->own_stream, cudaStreamNonBlocking));
     CK(cudaFuncSetAttribute(k_gap_head<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
     CK(cudaFuncSetAttribute(k_gap_head<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
-    { const char *e1 = getenv("KDL_GEMM_1CTA"); m->force_1cta = e1 && e1[0] == '1'; }
-    if ((rc = tc::configure(m->err)) != KDL_OK || (rc = tc2::configure2(m->err)) != KDL_OK || (rc = dwt::configure(m->err)) != KDL_OK) { set_err(g_err, "%s", m->err); kdl_destroy(m); return rc; }
+    { const char *e1 = getenv("KDL_GEMM_2CTA"); m->use_2cta = e1 && e1[0] == '1'; }
+    { const char *e1 = getenv("KDL_CONV2_TAPS"); m->conv_shifted_taps = e1 && e1[0] == '1'; }
+    if ((rc = tc::configure(m->err)) != KDL_OK || (rc = tc2::configure2(m->err)) != KDL_OK || (rc = convtc::configure(m->err)) != KDL_OK || (rc = dwt::configure(m->err)) != KDL_OK) { set_err(g_err, "%s", m->err); kdl_destroy(m); return rc; }
     *out = m;
     return KDL_OK;
 }
@@ -887,6 +902,16 @@ extern "C" int kdl_profile_end(KdlModel *m, KdlProfileRow *rows, int32_t capacit
         float t = 0.f;
         CK(cudaEventElapsedTime(&t, r.a, r.b));
         ms[r.cls] += t;
+    }
+    if (const char *path = getenv("KDL_PROFILE_DUMP")) {  // per-launch rows for offline analysis
+        if (FILE *f = fopen(path, "a")) {
+            for (auto &r : m->prof_recs) {
+                float t = 0.f;
+                cudaEventElapsedTime(&t, r.a, r.b);
+                fprintf(f, "%s;%s;%.6f;%.0f;%.0f\n", PROF_NAMES[r.cls], r.label, t, r.flops, r.bytes);
+            }
+            fclose(f);
+        }
     }
     int n = 0;
     for (int c = 0; c < PC_COUNT && n < capacity; ++c) {

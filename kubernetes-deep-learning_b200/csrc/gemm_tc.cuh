@@ -259,7 +259,7 @@ template <int SW, int BN, bool CONV>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
           const __grid_constant__ CUtensorMap tmOut, const float *__restrict__ bias, const bf16 *residual, bf16 *out, int M,
-          int N, int K, int relu, ConvGeom cg) {
+          int N, int K, int relu, ConvGeom cg, int ldo /*row pitch of out / residual in elements*/) {
     typedef Cfg<SW, BN, CONV> C;
     constexpr int STAGES = C::STAGES;
     constexpr int BK = C::BLOCK_K;
@@ -425,7 +425,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             } else {
                 // ---- standard: 64-column chunks -> swizzled smem -> TMA store; residual prefetched a chunk ahead ----
                 const bool row_ok = row < M;
-                const bf16 *res_row = residual + (size_t)row * N;
+                const bf16 *res_row = residual + (size_t)row * ldo;
                 uint4 rn[8];
                 auto load_res = [&](int c) {
 #pragma unroll
@@ -508,18 +508,21 @@ inline int num_sms() {
 }
 
 // standard GEMM: A [M,K] bf16 row-major, weights via tmB (box BLOCK_K x BLOCK_N over Wt[N,K]), out [M,N]
+// lda / ldo: row pitch (elements) of A and of out/residual; 0 = dense (K / N)
 inline int launch_gemm(const TmaEncoder &enc, const bf16 *A, const CUtensorMap *tmB, const float *bias, const bf16 *residual,
-                       bf16 *out, int M, int N, int K, int relu, cudaStream_t st, char *err) {
+                       bf16 *out, int M, int N, int K, int relu, cudaStream_t st, char *err, int lda = 0, int ldo = 0) {
+    if (lda == 0) lda = K;
+    if (ldo == 0) ldo = N;
     CUtensorMap tmA, tmOut;
-    if (!enc.encode_2d(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)K * 2, BLOCK_K, BLOCK_M, 128) ||
-        !enc.encode_2d(&tmOut, out, (uint64_t)N, (uint64_t)M, (uint64_t)N * 2, 64, 32, 128)) {
+    if (!enc.encode_2d(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, BLOCK_K, BLOCK_M, 128) ||
+        !enc.encode_2d(&tmOut, out, (uint64_t)N, (uint64_t)M, (uint64_t)ldo * 2, 64, 32, 128)) {
         snprintf(err, 512, "cuTensorMapEncodeTiled failed for A [%d,%d] / out [%d,%d]", M, K, M, N);
         return KDL_ECUDA;
     }
     const int tiles = ((M + BLOCK_M - 1) / BLOCK_M) * ((N + BLOCK_N - 1) / BLOCK_N);
     const int grid = tiles < num_sms() ? tiles : num_sms();
     k_gemm_tc<128, 256, false><<<grid, NUM_THREADS, CfgStd::SMEM_BYTES, st>>>(tmA, *tmB, tmOut, bias, residual, out, M, N, K, relu,
-                                                                              ConvGeom{0, 0, 0, 0});
+                                                                              ConvGeom{0, 0, 0, 0}, ldo);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         snprintf(err, 512, "k_gemm_tc launch (M=%d N=%d K=%d): %s", M, N, K, cudaGetErrorString(e));
@@ -542,7 +545,7 @@ inline int launch_conv3x3(const TmaEncoder &enc, const bf16 *in, const CUtensorM
     const int tiles = (M + BLOCK_M - 1) / BLOCK_M;
     const int grid = tiles < num_sms() ? tiles : num_sms();
     k_gemm_tc<64, 64, true><<<grid, NUM_THREADS, CfgConv::SMEM_BYTES, st>>>(tmA, *tmB, tmA /*unused*/, bias, nullptr, out, M, Cout,
-                                                                            9 * Cin, relu, ConvGeom{Hin, Win, Hin - 2, Win - 2});
+                                                                            9 * Cin, relu, ConvGeom{Hin, Win, Hin - 2, Win - 2}, Cout);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         snprintf(err, 512, "k_gemm_tc<conv> launch (B=%d H=%d): %s", B, Hin, cudaGetErrorString(e));

@@ -79,7 +79,7 @@ __device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 k_gemm_tc2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmOut,
-           const float *__restrict__ bias, const bf16 *residual, int M, int N, int K, int relu) {
+           const float *__restrict__ bias, const bf16 *residual, int M, int N, int K, int relu, int ldo) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // same offset in both CTAs (same kernel, same layout)
     const uint32_t epi_base = smem_base + STAGES2 * STAGE2_BYTES;
@@ -194,7 +194,7 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
             const int row = row0 + lane;
             const uint32_t t_row = tmem_base + acc * BN2 + ((uint32_t)(q * 32) << 16);
             const bool row_ok = row < M;
-            const bf16 *res_row = residual + (size_t)row * N;
+            const bf16 *res_row = residual + (size_t)row * ldo;
             uint4 rn[8];
             auto load_res = [&](int c) {
 #pragma unroll
@@ -259,17 +259,19 @@ inline int configure2(char *err) {
 
 // weights via tmB2: box 64 x 128 over Wt[N,K] (each CTA of the pair loads its half of the N tile)
 inline int launch_gemm2(const TmaEncoder &enc, const bf16 *A, const CUtensorMap *tmB2, const float *bias, const bf16 *residual, bf16 *out,
-                        int M, int N, int K, int relu, cudaStream_t st, char *err) {
+                        int M, int N, int K, int relu, cudaStream_t st, char *err, int lda = 0, int ldo = 0) {
+    if (lda == 0) lda = K;
+    if (ldo == 0) ldo = N;
     CUtensorMap tmA, tmOut;
-    if (!enc.encode_2d(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)K * 2, BK2, 128, 128) ||
-        !enc.encode_2d(&tmOut, out, (uint64_t)N, (uint64_t)M, (uint64_t)N * 2, 64, 32, 128)) {
+    if (!enc.encode_2d(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, BK2, 128, 128) ||
+        !enc.encode_2d(&tmOut, out, (uint64_t)N, (uint64_t)M, (uint64_t)ldo * 2, 64, 32, 128)) {
         snprintf(err, 512, "cuTensorMapEncodeTiled failed for A [%d,%d] / out [%d,%d]", M, K, M, N);
         return KDL_ECUDA;
     }
     const int tiles = ((M + 255) / 256) * ((N + BN2 - 1) / BN2);
     const int max_clusters = num_sms() / 2;
     const int clusters = tiles < max_clusters ? tiles : max_clusters;
-    k_gemm_tc2<<<2 * clusters, NUM_THREADS, SMEM2_BYTES, st>>>(tmA, *tmB2, tmOut, bias, residual, M, N, K, relu);
+    k_gemm_tc2<<<2 * clusters, NUM_THREADS, SMEM2_BYTES, st>>>(tmA, *tmB2, tmOut, bias, residual, M, N, K, relu, ldo);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         snprintf(err, 512, "k_gemm_tc2 launch (M=%d N=%d K=%d): %s", M, N, K, cudaGetErrorString(e));

@@ -198,7 +198,7 @@ k_dw3x3(const T *__restrict__ in, const float *__restrict__ w /*[9][C]*/, T *__r
 template <typename T>
 __global__ void __launch_bounds__(256)
 k_maxpool_add(const T *__restrict__ in, const T *__restrict__ res, T *__restrict__ out, int B, int H, int W,
-              int C, int Ho, int Wo, int pad_lo) {
+              int C, int ld /*pixel pitch in elements (>= C)*/, int Ho, int Wo, int pad_lo) {
     const int CV = C >> 3;  // 8 channels per thread
     long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     long long total = (long long)B * Ho * Wo * CV;
@@ -219,13 +219,13 @@ k_maxpool_add(const T *__restrict__ in, const T *__restrict__ res, T *__restrict
         for (int dx = 0; dx < 3; ++dx) {
             int iy = 2 * oy - pad_lo + dy, ix = 2 * ox - pad_lo + dx;
             bool ok = iy >= 0 && iy < H && ix >= 0 && ix < W;
-            const T *ptr = in + (((size_t)b * H + (ok ? iy : 0)) * W + (ok ? ix : 0)) * C + c;
+            const T *ptr = in + (((size_t)b * H + (ok ? iy : 0)) * W + (ok ? ix : 0)) * ld + c;
             v0[dy * 3 + dx] = m0;
             v1[dy * 3 + dx] = m0;
             if (ok) ld8<T>(ptr, v0[dy * 3 + dx], v1[dy * 3 + dx]);
         }
     }
-    size_t o = (((size_t)b * Ho + oy) * Wo + ox) * C + c;
+    size_t o = (((size_t)b * Ho + oy) * Wo + ox) * ld + c;
     float4 r0, r1;
     ld8<T>(res + o, r0, r1);
 #pragma unroll
@@ -237,7 +237,7 @@ k_maxpool_add(const T *__restrict__ in, const T *__restrict__ res, T *__restrict
 // seen as a dense [B*Ho*Wo, C] matrix (so the projection is a plain GEMM for the tcgen05 kernel).
 template <typename T>
 __global__ void __launch_bounds__(256)
-k_subsample2(const T *__restrict__ in, T *__restrict__ out, int B, int H, int W, int C, int Ho, int Wo) {
+k_subsample2(const T *__restrict__ in, T *__restrict__ out, int B, int H, int W, int C, int ld, int Ho, int Wo) {
     const int CV = C >> 2;
     long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     long long total = (long long)B * Ho * Wo * CV;
@@ -248,7 +248,7 @@ k_subsample2(const T *__restrict__ in, T *__restrict__ out, int B, int H, int W,
     long long q = p / Wo;
     int oy = (int)(q % Ho);
     int b = (int)(q / Ho);
-    V4<T>::st(out + p * C + cv * 4, V4<T>::ld(in + (((size_t)b * H + 2 * oy) * W + 2 * ox) * C + cv * 4));
+    V4<T>::st(out + p * ld + cv * 4, V4<T>::ld(in + (((size_t)b * H + 2 * oy) * W + 2 * ox) * ld + cv * 4));
 }
 
 // ---------------------------------------------------------------------------------------------------
