@@ -224,6 +224,24 @@ def main():
            "d2h_bytes_per_step": B * 10 * 4, "ms_per_step": e2e_s / K * 1e3,
            "api": "kdl_predict_u8_host (pinned host uint8 -> logits on host, synchronous)"}
 
+    # ---- batch-1 latency through the same host-facing call (BASELINE.json metric: "batch-1 p50 latency")
+    latency = None
+    if rank == 0:
+        one = engine.PackedImages(synth_images(1, S, 77), pinned=True)
+        h1 = np.empty((1, 10), np.float32)
+        for _ in range(20):
+            model.predict_packed_host(one, h1)
+        lat = []
+        for _ in range(300):
+            t0 = time.perf_counter()
+            model.predict_packed_host(one, h1)
+            lat.append((time.perf_counter() - t0) * 1e3)
+        lat.sort()
+        latency = {"p50_ms": lat[len(lat) // 2], "p99_ms": lat[int(len(lat) * 0.99)], "calls": len(lat),
+                   "launches_per_call": model.last_launch_count,
+                   "api": "kdl_predict_u8_host, batch 1, host pixels -> host logits (CUDA-graph replay of the forward)"}
+    barrier()
+
     # ---- per-kernel roofline: CUDA events around every launch, same steps, on the launching stream
     peaks = load_peaks()
     model.profile_begin()
@@ -259,6 +277,7 @@ def main():
                    "parallelism": f"replicas x{world} (no collective)",
                    "l2": f"{NSETS} input sets rotated; per-step activation working set (~{B * 155.1 / 1e3:.1f} GB at bs {B}) >> 126 MB L2"},
         "e2e": e2e, "gpu_launches": launches_per_step * K, "clocks": clk, "roofline": roof, "kernels": kernels,
+        "latency_b1": latency,
     }
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

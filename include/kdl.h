@@ -48,7 +48,7 @@ typedef struct KdlConfig {
     int32_t precision;    /* KDL_PRECISION_* */
     int32_t gemm_impl;    /* KDL_GEMM_* */
     int32_t keep_taps;    /* !=0: keep a copy of every tapped layer output for kdl_layer_output (debug; slow) */
-    int32_t reserved;
+    int32_t use_graphs;   /* !=0: replay the forward pass as a CUDA graph from the 3rd call with the same (batch, input buffer) on */
 } KdlConfig;
 
 /* Model lifecycle.  Replaces TF-Serving loading /models/clothing-model/1 at container start

@@ -23,7 +23,7 @@ STATIC_MAX_BATCH, STATIC_MAX_SIZE = 32, 512
 
 class KdlConfig(ctypes.Structure):
     _fields_ = [("device", c_int32), ("max_batch", c_int32), ("input_size", c_int32), ("head_inner", c_int32),
-                ("precision", c_int32), ("gemm_impl", c_int32), ("keep_taps", c_int32), ("reserved", c_int32)]
+                ("precision", c_int32), ("gemm_impl", c_int32), ("keep_taps", c_int32), ("use_graphs", c_int32)]
 
 
 class KdlProfileRow(ctypes.Structure):

@@ -132,6 +132,10 @@ struct KdlModel {
     std::vector<Tap> taps;
     tc::TmaEncoder tma;
 
+    // CUDA graphs of the forward pass, keyed by (batch, input pointer)
+    struct GraphEntry { int B; const float *in_f32; const uint8_t *in_u8; cudaGraphExec_t exec; int launches; };
+    std::vector<GraphEntry> graphs;
+
     // per-launch CUDA-event profiling (kdl_profile_begin / kdl_profile_end)
     bool profiling = false;
     struct ProfRec { int cls; cudaEvent_t a, b; double flops, bytes; char label[40]; };
@@ -672,6 +676,7 @@ extern "C" int kdl_destroy(KdlModel *m) {
     }
     if (m->own_stream) cudaStreamDestroy(m->own_stream);
     for (cudaEvent_t e : m->ev_pool) cudaEventDestroy(e);
+    for (auto &g : m->graphs) if (g.exec) cudaGraphExecDestroy(g.exec);
     delete m;
     return KDL_OK;
 }
@@ -740,14 +745,55 @@ extern "C" int kdl_preprocess_u8(KdlModel *m, const uint8_t *d_src, const int64_
     return KDL_OK;
 }
 
-static int run_forward(KdlModel *m, const float *in_f32, const uint8_t *in_u8, int B, float *d_logits, cudaStream_t st) {
-    m->last_B = B;
+static int run_forward_eager(KdlModel *m, const float *in_f32, const uint8_t *in_u8, int B, float *d_logits, cudaStream_t st) {
     if (m->cfg.precision == KDL_PRECISION_F32) {
         Runner<float> r{m, st, B};
         return r.forward(in_f32, in_u8, d_logits);
     }
     Runner<bf16> r{m, st, B};
     return r.forward(in_f32, in_u8, d_logits);
+}
+
+// The forward pass is a fixed sequence of ~85 launches whose arguments (arena pointers, TMA descriptors passed by value) depend
+// only on (batch, input pointer).  With cfg.use_graphs the second call with a given key captures that sequence into a CUDA graph
+// (on the model's own stream) and later calls replay it on the caller's stream: what matters for batch-1 latency, where the
+// ~30 us of device work would otherwise sit behind ~400 us of launch overhead.  The graph writes to the model's logits buffer.
+static int run_forward(KdlModel *m, const float *in_f32, const uint8_t *in_u8, int B, float *d_logits, cudaStream_t st) {
+    m->last_B = B;
+    char *err = m->err;
+    if (!m->cfg.use_graphs || m->cfg.keep_taps || m->profiling) return run_forward_eager(m, in_f32, in_u8, B, d_logits, st);
+    KdlModel::GraphEntry *ge = nullptr;
+    for (auto &g : m->graphs)
+        if (g.B == B && g.in_f32 == in_f32 && g.in_u8 == in_u8) { ge = &g; break; }
+    if (!ge) {  // first sighting: run eagerly (also finishes any lazy initialisation), remember the key
+        if (m->graphs.size() >= 16) {
+            for (auto &g : m->graphs) if (g.exec) { cudaGraphExecDestroy(g.exec); }
+            m->graphs.clear();
+        }
+        KdlModel::GraphEntry g;
+        g.B = B; g.in_f32 = in_f32; g.in_u8 = in_u8; g.exec = nullptr; g.launches = 0;
+        m->graphs.push_back(g);
+        return run_forward_eager(m, in_f32, in_u8, B, d_logits, st);
+    }
+    if (!ge->exec) {
+        const int before = m->launches;
+        cudaGraph_t graph = nullptr;
+        CK(cudaStreamBeginCapture(m->own_stream, cudaStreamCaptureModeThreadLocal));
+        int rc = run_forward_eager(m, in_f32, in_u8, B, m->d_logits, m->own_stream);
+        cudaError_t e = cudaStreamEndCapture(m->own_stream, &graph);
+        if (rc != KDL_OK) { if (graph) cudaGraphDestroy(graph); return rc; }
+        if (e != cudaSuccess) { set_err(err, "cudaStreamEndCapture -> %s", cudaGetErrorString(e)); return KDL_ECUDA; }
+        e = cudaGraphInstantiate(&ge->exec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (e != cudaSuccess) { ge->exec = nullptr; set_err(err, "cudaGraphInstantiate -> %s", cudaGetErrorString(e)); return KDL_ECUDA; }
+        ge->launches = m->launches - before;
+        m->launches = before;
+    }
+    CK(cudaGraphLaunch(ge->exec, st));
+    m->launches += ge->launches;
+    if (d_logits != m->d_logits)
+        CK(cudaMemcpyAsync(d_logits, m->d_logits, (size_t)B * 10 * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    return KDL_OK;
 }
 
 extern "C" int kdl_forward(KdlModel *m, const float *d_input_8, int32_t B, float *d_dense_7, void *stream) {

@@ -58,7 +58,7 @@ class PackedImages:
 class Model:
     def __init__(self, weights: Dict[str, np.ndarray], device: int = 0, max_batch: int = 64, input_size: int = 299,
                  precision: str = "bf16", gemm_impl: str = "auto", keep_taps: bool = False,
-                 head_inner: Optional[int] = None):
+                 head_inner: Optional[int] = None, use_graphs: bool = True):
         if not torch.cuda.is_available():
             raise RuntimeError("kdl_b200.Model needs a CUDA device (B200, sm_100a); there is no CPU fallback")
         self.lib = _lib.load()
@@ -72,7 +72,7 @@ class Model:
         cfg = _lib.KdlConfig(device=device, max_batch=max_batch, input_size=input_size, head_inner=head_inner,
                              precision={"f32": _lib.PRECISION_F32, "bf16": _lib.PRECISION_BF16}[precision],
                              gemm_impl={"auto": _lib.GEMM_AUTO, "simple": _lib.GEMM_SIMPLE}[gemm_impl],
-                             keep_taps=int(keep_taps), reserved=0)
+                             keep_taps=int(keep_taps), use_graphs=int(use_graphs and not keep_taps))
         h = ctypes.c_void_p()
         torch.cuda.init()
         with torch.cuda.device(device):

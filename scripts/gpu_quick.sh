@@ -8,7 +8,7 @@ python - <<'PY'
 import json
 try:
     d=json.load(open('gpurun_out/q_bench.json'))
-    print('value',round(d['value'],1),'e2e',round(d['e2e']['value'],1),'ms/step',round(d['ms_per_step'],3))
+    print('value',round(d['value'],1),'e2e',round(d['e2e']['value'],1),'ms/step',round(d['ms_per_step'],3),'lat',d.get('latency_b1'))
     for k in d['kernels']: print(f"  {k['kernel']:<34} n={k['launches_per_step']:3d} {k['ms_per_step']:8.3f} ms {100*k['share']:5.1f}%  {k['achieved_tflops']:8.1f} TF {k['achieved_gbs']:8.1f} GB/s frac {k['frac']:.3f}")
 except Exception as e: print('no bench json',e)
 PY
