@@ -18,6 +18,7 @@
 #include "gemm_tc2.cuh"
 #include "conv_tc.cuh"
 #include "dw_tma.cuh"
+#include "pool_tma.cuh"
 #include "kernels.cuh"
 
 using namespace kdl;
@@ -285,8 +286,9 @@ template <typename T> struct Runner {
     }
 
     // Conv2D(1x1, strides 2, 'same') + BN : residual projection.  in: [B,H,H,Cin] -> out [B,Ho,Ho,Cout]
-    int projection(const T *in, const GemmW &g, T *out, int H, int Ho) {
+    int projection(const T *in, const GemmW &g, T *out, int H, int Ho, bool have_sub = false) {
         int M = B * Ho * Ho;
+        if (use_tc() && have_sub) return gemm((const T *)m->S, g, nullptr, out, M, 0, RowMap{0, 0, 0, 0, 0, 0});
         if (use_tc() && tc::shape_supported(M, g.N, g.K)) {
             long long total = (long long)M * (g.K / 4);
             prof_open(m, st, PC_SUBSAMPLE, 0.0, 2.0 * M * g.K * sizeof(T));
@@ -298,12 +300,21 @@ template <typename T> struct Runner {
         return gemm(in, g, nullptr, out, M, 0, RowMap{1, H, H, Ho, Ho, g.K});
     }
 
-    int pool_add(const T *in, const T *resid, T *out, int H, int C, int Ho) {
+    // sub != nullptr: also write the even-index pixels of the result compactly (input of the next strided projection)
+    int pool_add(const T *in, const T *resid, T *out, T *sub, int H, int C, int Ho) {
         int pad_total = (Ho - 1) * 2 + 3 - H;
         if (pad_total < 0) pad_total = 0;
         int pad_lo = pad_total / 2;  // TF SAME: extra padding goes to the end
-        long long total = (long long)B * Ho * Ho * (C / 4);
         prof_open(m, st, PC_POOL, 0.0, ((double)B * H * H * C + 2.0 * B * Ho * Ho * C) * sizeof(T), "pool H=%d C=%d", H, C);
+        if (use_tc()) {
+            int rc = poolt::launch(m->tma, (const bf16 *)in, (const bf16 *)resid, (bf16 *)out, (bf16 *)sub, B, H, H, C, ld(C), Ho, Ho, pad_lo,
+                                   st, m->err);
+            prof_close(m, st);
+            if (rc != KDL_OK) return rc;
+            m->launches++;
+            return KDL_OK;
+        }
+        long long total = (long long)B * Ho * Ho * (C / 8);
         k_maxpool_add<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(in, resid, out, B, H, H, C, ld(C), Ho, Ho, pad_lo);
         prof_close(m, st);
         LAUNCH_CHECK();
@@ -350,9 +361,10 @@ template <typename T> struct Runner {
         }
         // ---- entry/exit blocks with projection + pool: 2,3,4 then middle, then 13 ----
         int si = 0;  // sepconv index
+        bool have_sub = false;  // S already holds the even pixels of X (written by the previous block's pool kernel)
         auto entry_block = [&](int blk, int ri, int H, int Ho) -> int {
             const GemmW &rg = m->res[ri];
-            RUN(projection(X, rg, R, H, Ho));
+            RUN(projection(X, rg, R, H, Ho, have_sub));
             snprintf(name, sizeof name, "block%d_res_bn", blk);
             RUN(tap(name, R, Ho, rg.N, 0));
             // sepconv1: ReLU on load except block2 (input is already post-ReLU there)
@@ -367,7 +379,10 @@ template <typename T> struct Runner {
             RUN(tap(name, U, H, m->pw[si].N, 0));
             int C = m->pw[si].N;
             ++si;
-            RUN(pool_add(U, R, X, H, C, Ho));
+            // blocks 2 and 3 feed another strided projection: let the pool kernel emit its input (tensor-core path only)
+            const bool emit_sub = use_tc() && (blk == 2 || blk == 3);
+            RUN(pool_add(U, R, X, emit_sub ? (T *)m->S : nullptr, H, C, Ho));
+            have_sub = emit_sub;
             snprintf(name, sizeof name, "block%d_out", blk);
             RUN(tap(name, X, Ho, C, 0));
             return KDL_OK;
@@ -659,7 +674,7 @@ extern "C" int kdl_create(const KdlConfig *cfg, KdlModel **out) {
     CK(cudaFuncSetAttribute(k_gap_head<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
     { const char *e1 = getenv("KDL_GEMM_2CTA"); m->use_2cta = e1 && e1[0] == '1'; }
     { const char *e1 = getenv("KDL_CONV2_TAPS"); m->conv_shifted_taps = e1 && e1[0] == '1'; }
-    if ((rc = tc::configure(m->err)) != KDL_OK || (rc = tc2::configure2(m->err)) != KDL_OK || (rc = convtc::configure(m->err)) != KDL_OK || (rc = dwt::configure(m->err)) != KDL_OK) { set_err(g_err, "%s", m->err); kdl_destroy(m); return rc; }
+    if ((rc = tc::configure(m->err)) != KDL_OK || (rc = tc2::configure2(m->err)) != KDL_OK || (rc = convtc::configure(m->err)) != KDL_OK || (rc = dwt::configure(m->err)) != KDL_OK || (rc = poolt::configure(m->err)) != KDL_OK) { set_err(g_err, "%s", m->err); kdl_destroy(m); return rc; }
     *out = m;
     return KDL_OK;
 }
