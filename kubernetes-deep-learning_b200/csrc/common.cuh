@@ -70,6 +70,16 @@ template <typename T> __device__ __forceinline__ void st1(T *p, float v);
 template <> __device__ __forceinline__ void st1<float>(float *p, float v) { *p = v; }
 template <> __device__ __forceinline__ void st1<bf16>(bf16 *p, float v) { *p = __float2bfloat16_rn(v); }
 
+// packed fp32 FMA (Blackwell FFMA2): d = a * b + c on two lanes
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+    unsigned long long d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;"
+        : "=l"(d)
+        : "l"(*reinterpret_cast<unsigned long long *>(&a)), "l"(*reinterpret_cast<unsigned long long *>(&b)),
+          "l"(*reinterpret_cast<unsigned long long *>(&c)));
+    return *reinterpret_cast<float2 *>(&d);
+}
+
 __device__ __forceinline__ float4 relu4(float4 v) {
     return make_float4(fmaxf(v.x, 0.f), fmaxf(v.y, 0.f), fmaxf(v.z, 0.f), fmaxf(v.w, 0.f));
 }

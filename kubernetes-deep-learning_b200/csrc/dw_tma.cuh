@@ -18,6 +18,9 @@
 namespace kdl {
 namespace dwt {
 
+#ifndef KDL_STREAM_STORES
+#define KDL_STREAM_STORES 0
+#endif
 constexpr int STAGES = 3;
 constexpr int CB = 64;                       // channels per tile
 constexpr uint32_t W_BYTES = 9 * CB * 4;     // fp32 weights of one chunk: [9][64]
@@ -78,15 +81,13 @@ __device__ __forceinline__ void bulk_load_1d(uint32_t dst, const void *src, uint
                  "r"(bytes), "r"(bar)
                  : "memory");
 }
-__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
-    unsigned long long d;
-    asm("fma.rn.f32x2 %0, %1, %2, %3;"
-        : "=l"(d)
-        : "l"(*reinterpret_cast<unsigned long long *>(&a)), "l"(*reinterpret_cast<unsigned long long *>(&b)),
-          "l"(*reinterpret_cast<unsigned long long *>(&c)));
-    return *reinterpret_cast<float2 *>(&d);
-}
 __device__ __forceinline__ float2 fmul2(float2 a, float2 b) { return make_float2(a.x * b.x, a.y * b.y); }
+
+// streaming (evict-first) 8-byte store: the output is far larger than L2 and is next read by another kernel
+__device__ __forceinline__ void st_stream(bf16 *p, uint2 v) {
+    if (KDL_STREAM_STORES) asm volatile("st.global.cs.v2.b32 [%0], {%1, %2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
+    else *reinterpret_cast<uint2 *>(p) = v;
+}
 
 struct Px {  // 4 channels of one pixel in fp32
     float2 lo, hi;
@@ -225,8 +226,8 @@ k_dw_tma(const __grid_constant__ CUtensorMap tmIn, const float *__restrict__ wpa
                 uint2 v0, v1;
                 v0.x = tc::pack_bf16(aA[0][0].x, aA[0][0].y); v0.y = tc::pack_bf16(aA[0][1].x, aA[0][1].y);
                 v1.x = tc::pack_bf16(aA[1][0].x, aA[1][0].y); v1.y = tc::pack_bf16(aA[1][1].x, aA[1][1].y);
-                *reinterpret_cast<uint2 *>(o) = v0;
-                if (st1) *reinterpret_cast<uint2 *>(o + p.ld) = v1;
+                st_stream(o, v0);
+                if (st1) st_stream(o + p.ld, v1);
                 o += orow;
             };
             auto rotate = [&]() {

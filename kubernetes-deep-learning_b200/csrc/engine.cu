@@ -98,6 +98,7 @@ struct KdlModel {
     KdlConfig cfg;
     char err[512];
     bool weights_loaded = false;
+    int microbatch_mb = 0;           // KDL_MICROBATCH_MB: size (MiB) of the L2-resident depthwise->pointwise hand-off, 0 = off
     bool conv_shifted_taps = false;  // KDL_CONV2_TAPS=1: 9 shifted TMA boxes per tile instead of the staged halo (A/B)
     bool use_2cta = false;    // KDL_GEMM_2CTA=1: CTA-pair (cta_group::2) kernel for the K>=512 layers (A/B measurements)
     int launches = 0;
@@ -198,6 +199,12 @@ static int find_tap(KdlModel *m, const char *name) {
     return -1;
 }
 
+#define RUN(x)                          \
+    do {                                \
+        int rc_ = (x);                  \
+        if (rc_ != KDL_OK) return rc_;  \
+    } while (0)
+
 template <typename T> struct Runner {
     KdlModel *m;
     cudaStream_t st;
@@ -232,7 +239,8 @@ template <typename T> struct Runner {
         return KDL_OK;
     }
 
-    int dwconv(const T *in, const float *w, const float *wpad, T *out, int H, int C, int relu_in) {
+    int dwconv(const T *in, const float *w, const float *wpad, T *out, int H, int C, int relu_in, int nb = -1) {
+        const int B = nb < 0 ? this->B : nb;
         int rows = H >= 64 ? 8 : (H >= 16 ? 5 : H);
         int vec = H * (C / 4);
         dim3 grid((vec + 127) / 128, (H + rows - 1) / rows, B);
@@ -285,6 +293,30 @@ template <typename T> struct Runner {
         return KDL_OK;
     }
 
+    // depthwise -> pointwise of one SeparableConv2D.  For the big early layers (K <= 256, HBM-bound) the batch is walked in
+    // micro-batches that all reuse the SAME small region of the T buffer: the depthwise output of micro-batch i is consumed by
+    // its GEMM while still in L2 and overwritten by micro-batch i+1 before it is ever written back, so the intermediate tensor
+    // costs (almost) no HBM traffic.
+    int sepconv(const T *in, int si, T *out, int H, int relu_in, int relu_out) {
+        const GemmW &g = m->pw[si];
+        const RowMap dense{0, 0, 0, 0, 0, 0};
+        T *Tb = (T *)m->T;
+        int mb = B;
+        if (use_tc() && m->microbatch_mb > 0 && g.K <= 256) {
+            size_t per_img = (size_t)H * H * ld(g.K) * sizeof(T);
+            mb = (int)((size_t)m->microbatch_mb * (1u << 20) / per_img);
+            if (mb < 1) mb = 1;
+            if (mb > B) mb = B;
+        }
+        for (int b0 = 0; b0 < B; b0 += mb) {
+            const int nb = (B - b0) < mb ? (B - b0) : mb;
+            const size_t ioff = (size_t)b0 * H * H * ld(g.K), ooff = (size_t)b0 * H * H * ld(g.N);
+            RUN(dwconv(in + ioff, m->dw[si], m->dwpad[si], Tb, H, g.K, relu_in, nb));
+            RUN(gemm(Tb, g, nullptr, out + ooff, nb * H * H, relu_out, dense));
+        }
+        return KDL_OK;
+    }
+
     // Conv2D(1x1, strides 2, 'same') + BN : residual projection.  in: [B,H,H,Cin] -> out [B,Ho,Ho,Cout]
     int projection(const T *in, const GemmW &g, T *out, int H, int Ho, bool have_sub = false) {
         int M = B * Ho * Ho;
@@ -321,11 +353,6 @@ template <typename T> struct Runner {
         return KDL_OK;
     }
 
-#define RUN(x)                          \
-    do {                                \
-        int rc_ = (x);                  \
-        if (rc_ != KDL_OK) return rc_;  \
-    } while (0)
 
     // in_f32: serving_default tensor, or in_u8: resized uint8 batch (exactly one non-null)
     int forward(const float *in_f32, const uint8_t *in_u8, float *d_logits) {
@@ -368,13 +395,12 @@ template <typename T> struct Runner {
             snprintf(name, sizeof name, "block%d_res_bn", blk);
             RUN(tap(name, R, Ho, rg.N, 0));
             // sepconv1: ReLU on load except block2 (input is already post-ReLU there)
-            RUN(dwconv(X, m->dw[si], m->dwpad[si], Tb, H, m->pw[si].K, blk != 2));
-            RUN(gemm(Tb, m->pw[si], nullptr, U, B * H * H, 1, dense));  // next sepconv's ReLU folded here
+            RUN(sepconv(X, si, U, H, blk != 2, 1));  // next sepconv's ReLU folded into this GEMM's epilogue
             snprintf(name, sizeof name, "block%d_sepconv1_bn", blk);
             RUN(tap(name, U, H, m->pw[si].N, 1));
             ++si;
-            RUN(dwconv(U, m->dw[si], m->dwpad[si], Tb, H, m->pw[si].K, 0));
-            RUN(gemm(Tb, m->pw[si], nullptr, U, B * H * H, 0, dense));
+            // in-place U -> T -> U is fine per micro-batch: the GEMM of micro-batch i only overwrites U rows already consumed
+            RUN(sepconv(U, si, U, H, 0, 0));
             snprintf(name, sizeof name, "block%d_sepconv2_bn", blk);
             RUN(tap(name, U, H, m->pw[si].N, 0));
             int C = m->pw[si].N;
@@ -674,6 +700,7 @@ extern "C" int kdl_create(const KdlConfig *cfg, KdlModel **out) {
     CK(cudaFuncSetAttribute(k_gap_head<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
     { const char *e1 = getenv("KDL_GEMM_2CTA"); m->use_2cta = e1 && e1[0] == '1'; }
     { const char *e1 = getenv("KDL_CONV2_TAPS"); m->conv_shifted_taps = e1 && e1[0] == '1'; }
+    { const char *e1 = getenv("KDL_MICROBATCH_MB"); m->microbatch_mb = e1 ? atoi(e1) : 0; }
     if ((rc = tc::configure(m->err)) != KDL_OK || (rc = tc2::configure2(m->err)) != KDL_OK || (rc = convtc::configure(m->err)) != KDL_OK || (rc = dwt::configure(m->err)) != KDL_OK || (rc = poolt::configure(m->err)) != KDL_OK) { set_err(g_err, "%s", m->err); kdl_destroy(m); return rc; }
     *out = m;
     return KDL_OK;
@@ -754,7 +781,7 @@ extern "C" int kdl_preprocess_u8(KdlModel *m, const uint8_t *d_src, const int64_
     int S = m->cfg.input_size;
     long long total = (long long)B * S * S * 3;
     prof_open(m, st, PC_RESIZE, 0.0, 5.0 * total);
-    k_resize<float><<<(unsigned)((total / 4 + 256) / 256), 256, 0, st>>>(d_src, dm, m->d_xtab, m->d_ytab, B, S, d_out);
+    k_resize<float><<<dim3(S, B), 128, ((S * 3 + 15) & ~15) + 1024, st>>>(d_src, dm, m->d_xtab, m->d_ytab, B, S, d_out);
     prof_close(m, st);
     LAUNCH_CHECK();
     return KDL_OK;
@@ -832,7 +859,7 @@ extern "C" int kdl_predict_u8(KdlModel *m, const uint8_t *d_src, const int64_t *
     long long total = (long long)B * S * S * 3;
     // resized uint8 stays 1 byte/px; the x/127.5-1 scaling is applied (bit-exactly) inside block1_conv1's load
     prof_open(m, st, PC_RESIZE, 0.0, 2.0 * total);
-    k_resize<uint8_t><<<(unsigned)((total / 4 + 256) / 256), 256, 0, st>>>(d_src, dm, m->d_xtab, m->d_ytab, B, S, m->u8img);
+    k_resize<uint8_t><<<dim3(S, B), 128, ((S * 3 + 15) & ~15) + 1024, st>>>(d_src, dm, m->d_xtab, m->d_ytab, B, S, m->u8img);
     prof_close(m, st);
     LAUNCH_CHECK();
     return run_forward(m, nullptr, m->u8img, B, d_dense_7, st);

@@ -33,15 +33,19 @@ constexpr int NUM_THREADS = 192;
 constexpr int BLOCK_N = 256;  // standard configuration (weight tensor-map box rows)
 constexpr int BLOCK_K = 64;   // standard configuration: 64 bf16 = 128 bytes = one swizzle-128B row
 
-template <int SW, int BN, bool CONV> struct Cfg {
+// NST = operand ring depth, EB = output staging buffers per epilogue warp.  Tensor-bound layers want a deep operand ring
+// (4 x 48 KB) and get by with 2 store buffers; the HBM-bound K<=256 layers are limited by TMA stores in flight, so they trade
+// one ring stage for 4 store buffers per warp.
+template <int SW, int BN, bool CONV, int NST = (CONV ? 12 : 4), int EB = 2> struct Cfg {
     static constexpr int BLOCK_N = BN;
     static constexpr int BLOCK_K = SW / 2;  // elements per k-block = one swizzle row
-    static constexpr int STAGES = CONV ? 12 : 4;
+    static constexpr int STAGES = NST;
+    static constexpr int EPI_BUFS = EB;
     static constexpr uint32_t A_BYTES = BLOCK_M * SW;
     static constexpr uint32_t B_BYTES = CONV ? 0 : BN * SW;           // conv mode keeps all 9 weight taps resident instead
     static constexpr uint32_t W_RES_BYTES = CONV ? 9 * BN * SW : 0;   // 9 taps x [64 out-ch x 32 in-ch] bf16 = 36 KB
     static constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr uint32_t EPI_BYTES = CONV ? 0 : 4 * 2 * 4096;  // per epilogue warp: 2 x (32 rows x 128 B)
+    static constexpr uint32_t EPI_BYTES = CONV ? 0 : 4 * EB * 4096;  // per epilogue warp: EB x (32 rows x 128 B)
     static constexpr uint32_t BIAS_BYTES = BN * 4;
     static constexpr uint32_t BAR_BYTES = 256;
     static constexpr uint32_t SMEM_BYTES = STAGES * STAGE_BYTES + W_RES_BYTES + EPI_BYTES + BIAS_BYTES + BAR_BYTES + 1024 /*align slack*/;
@@ -50,6 +54,7 @@ template <int SW, int BN, bool CONV> struct Cfg {
     static_assert(2 * BN <= 512, "two accumulators must fit the 512 TMEM columns");
 };
 typedef Cfg<128, 256, false> CfgStd;
+typedef Cfg<128, 256, false, 3, 4> CfgHbm;
 typedef Cfg<64, 64, true> CfgConv;
 
 // geometry of the implicit-GEMM conv mode (ignored otherwise)
@@ -228,39 +233,49 @@ __device__ __forceinline__ float4 ld_shared_f4(uint32_t addr) {
     return v;
 }
 
-// bias (+ReLU) (+residual) on 8 accumulator columns -> one 16-byte bf16 vector
+// bias (+ReLU) (+residual) on 8 accumulator columns -> one 16-byte bf16 vector.  Instruction-lean on purpose (the epilogue of the
+// HBM-bound K<=256 layers is issue-bound): packed fp32 adds (add.f32x2), ReLU as one packed bf16x2 max per pair AFTER rounding
+// (max commutes with round-to-nearest), residual added in fp32 before the rounding.
+__device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
+    unsigned long long d;
+    asm("add.rn.f32x2 %0, %1, %2;"
+        : "=l"(d)
+        : "l"(*reinterpret_cast<unsigned long long *>(&a)), "l"(*reinterpret_cast<unsigned long long *>(&b)));
+    return *reinterpret_cast<float2 *>(&d);
+}
 __device__ __forceinline__ uint4 epi8(const uint32_t *acc, uint32_t bias_addr, int relu, bool has_res, uint4 rr) {
     const float4 b0 = ld_shared_f4(bias_addr), b1 = ld_shared_f4(bias_addr + 16);
-    float v[8];
-    v[0] = __uint_as_float(acc[0]) + b0.x; v[1] = __uint_as_float(acc[1]) + b0.y;
-    v[2] = __uint_as_float(acc[2]) + b0.z; v[3] = __uint_as_float(acc[3]) + b0.w;
-    v[4] = __uint_as_float(acc[4]) + b1.x; v[5] = __uint_as_float(acc[5]) + b1.y;
-    v[6] = __uint_as_float(acc[6]) + b1.z; v[7] = __uint_as_float(acc[7]) + b1.w;
-    if (relu) {
-#pragma unroll
-        for (int j = 0; j < 8; ++j) v[j] = fmaxf(v[j], 0.f);
-    }
+    float2 v0 = fadd2(make_float2(__uint_as_float(acc[0]), __uint_as_float(acc[1])), make_float2(b0.x, b0.y));
+    float2 v1 = fadd2(make_float2(__uint_as_float(acc[2]), __uint_as_float(acc[3])), make_float2(b0.z, b0.w));
+    float2 v2 = fadd2(make_float2(__uint_as_float(acc[4]), __uint_as_float(acc[5])), make_float2(b1.x, b1.y));
+    float2 v3 = fadd2(make_float2(__uint_as_float(acc[6]), __uint_as_float(acc[7])), make_float2(b1.z, b1.w));
     if (has_res) {
-        v[0] += __uint_as_float(rr.x << 16); v[1] += __uint_as_float(rr.x & 0xffff0000u);
-        v[2] += __uint_as_float(rr.y << 16); v[3] += __uint_as_float(rr.y & 0xffff0000u);
-        v[4] += __uint_as_float(rr.z << 16); v[5] += __uint_as_float(rr.z & 0xffff0000u);
-        v[6] += __uint_as_float(rr.w << 16); v[7] += __uint_as_float(rr.w & 0xffff0000u);
+        v0 = fadd2(v0, make_float2(__uint_as_float(rr.x << 16), __uint_as_float(rr.x & 0xffff0000u)));
+        v1 = fadd2(v1, make_float2(__uint_as_float(rr.y << 16), __uint_as_float(rr.y & 0xffff0000u)));
+        v2 = fadd2(v2, make_float2(__uint_as_float(rr.z << 16), __uint_as_float(rr.z & 0xffff0000u)));
+        v3 = fadd2(v3, make_float2(__uint_as_float(rr.w << 16), __uint_as_float(rr.w & 0xffff0000u)));
     }
     uint4 o;
-    o.x = pack_bf16(v[0], v[1]); o.y = pack_bf16(v[2], v[3]);
-    o.z = pack_bf16(v[4], v[5]); o.w = pack_bf16(v[6], v[7]);
+    o.x = pack_bf16(v0.x, v0.y); o.y = pack_bf16(v1.x, v1.y);
+    o.z = pack_bf16(v2.x, v2.y); o.w = pack_bf16(v3.x, v3.y);
+    if (relu) {
+        asm("max.bf16x2 %0, %0, %1;" : "+r"(o.x) : "r"(0u));
+        asm("max.bf16x2 %0, %0, %1;" : "+r"(o.y) : "r"(0u));
+        asm("max.bf16x2 %0, %0, %1;" : "+r"(o.z) : "r"(0u));
+        asm("max.bf16x2 %0, %0, %1;" : "+r"(o.w) : "r"(0u));
+    }
     return o;
 }
 
 // ---------------------------------------------------------------------------------------------------
 // the kernel
 // ---------------------------------------------------------------------------------------------------
-template <int SW, int BN, bool CONV>
+template <int SW, int BN, bool CONV, int NST = (CONV ? 12 : 4), int EB = 2>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
           const __grid_constant__ CUtensorMap tmOut, const float *__restrict__ bias, const bf16 *residual, bf16 *out, int M,
           int N, int K, int relu, ConvGeom cg, int ldo /*row pitch of out / residual in elements*/) {
-    typedef Cfg<SW, BN, CONV> C;
+    typedef Cfg<SW, BN, CONV, NST, EB> C;
     constexpr int STAGES = C::STAGES;
     constexpr int BK = C::BLOCK_K;
     extern __shared__ uint8_t smem_raw[];
@@ -365,9 +380,10 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         // ================= epilogue: warps 2..5; TMEM lane quarter = warp % 4 =================
         const int q = warp & 3;
         const int et = threadIdx.x - 64;  // 0..127
-        const uint32_t ebuf = epi_base + (uint32_t)(warp - 2) * 8192u;
+        const uint32_t ebuf = epi_base + (uint32_t)(warp - 2) * (uint32_t)(C::EPI_BUFS * 4096);
         const bool has_res = residual != nullptr;
         int staged_n0 = -1, pref_n0 = -1;
+        uint32_t chunk_no = 0;
         float bpre[(BN + 127) / 128];
         int it = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
@@ -448,9 +464,9 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
 #pragma unroll
                         for (int g = 0; g < 8; ++g) rc[g] = rn[g];
                         if (has_res && c + 1 < BN / 64 && nc + 64 < N) load_res(c + 1);
-                        const uint32_t buf = ebuf + (uint32_t)(c & 1) * 4096u;
+                        const uint32_t buf = ebuf + (uint32_t)(chunk_no++ % C::EPI_BUFS) * 4096u;  // ring over ALL chunks of all tiles
                         // the TMA store issued two chunks ago from this buffer must have finished reading it
-                        if (lane == 0) bulk_wait_read<1>();
+                        if (lane == 0) bulk_wait_read<C::EPI_BUFS - 1>();
                         __syncwarp();
                         tmem_ld_wait();
 #pragma unroll
@@ -488,6 +504,8 @@ inline int configure(char *err) {
     cudaError_t e = cudaFuncSetAttribute(k_gemm_tc<128, 256, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)CfgStd::SMEM_BYTES);
     if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(k_gemm_tc<128, 256, false, 3, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CfgHbm::SMEM_BYTES);
+    if (e == cudaSuccess)
         e = cudaFuncSetAttribute(k_gemm_tc<64, 64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CfgConv::SMEM_BYTES);
     if (e != cudaSuccess) {
         snprintf(err, 512, "cudaFuncSetAttribute(k_gemm_tc smem): %s", cudaGetErrorString(e));
@@ -521,8 +539,12 @@ inline int launch_gemm(const TmaEncoder &enc, const bf16 *A, const CUtensorMap *
     }
     const int tiles = ((M + BLOCK_M - 1) / BLOCK_M) * ((N + BLOCK_N - 1) / BLOCK_N);
     const int grid = tiles < num_sms() ? tiles : num_sms();
-    k_gemm_tc<128, 256, false><<<grid, NUM_THREADS, CfgStd::SMEM_BYTES, st>>>(tmA, *tmB, tmOut, bias, residual, out, M, N, K, relu,
-                                                                              ConvGeom{0, 0, 0, 0}, ldo);
+    if (K <= 256)  // HBM-bound: more stores in flight matter more than ring depth
+        k_gemm_tc<128, 256, false, 3, 4><<<grid, NUM_THREADS, CfgHbm::SMEM_BYTES, st>>>(tmA, *tmB, tmOut, bias, residual, out, M, N, K,
+                                                                                        relu, ConvGeom{0, 0, 0, 0}, ldo);
+    else
+        k_gemm_tc<128, 256, false><<<grid, NUM_THREADS, CfgStd::SMEM_BYTES, st>>>(tmA, *tmB, tmOut, bias, residual, out, M, N, K, relu,
+                                                                                  ConvGeom{0, 0, 0, 0}, ldo);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         snprintf(err, 512, "k_gemm_tc launch (M=%d N=%d K=%d): %s", M, N, K, cudaGetErrorString(e));

@@ -34,54 +34,58 @@ __global__ void k_index_tables(const ImgMeta *__restrict__ meta, int B, int S, i
     }
 }
 
-// Gather + (optional) scale.  Flat over the B*S*S*3 output elements, 4 consecutive elements per thread so the
-// store is one aligned 16-byte (float) or 4-byte (uint8) vector and a warp writes 512 / 128 contiguous bytes.
+// Gather + (optional) scale.
 template <typename TOut> struct PxOut;
-template <> struct PxOut<float> {
-    static __device__ __forceinline__ float cvt(uint8_t v) { return scale_px(v); }
-    static __device__ __forceinline__ void st4(float *p, float a, float b, float c, float d) {
-        *reinterpret_cast<float4 *>(p) = make_float4(a, b, c, d);
+template <> struct PxOut<float> {  // scaled: the gateway's x/127.5-1 through an exact 256-entry table
+    static __device__ __forceinline__ float cvt1(uint8_t v, const float *lut) { return lut[v]; }
+    static __device__ __forceinline__ void st16(float *p, const uint8_t *s, const float *lut) {
+        *reinterpret_cast<float4 *>(p) = make_float4(lut[s[0]], lut[s[1]], lut[s[2]], lut[s[3]]);
     }
 };
-template <> struct PxOut<uint8_t> {
-    static __device__ __forceinline__ uint8_t cvt(uint8_t v) { return v; }
-    static __device__ __forceinline__ void st4(uint8_t *p, uint8_t a, uint8_t b, uint8_t c, uint8_t d) {
-        *reinterpret_cast<uchar4 *>(p) = make_uchar4(a, b, c, d);
+template <> struct PxOut<uint8_t> {  // raw bytes (scaling is applied inside block1_conv1's load)
+    static __device__ __forceinline__ uint8_t cvt1(uint8_t v, const float *) { return v; }
+    static __device__ __forceinline__ void st16(uint8_t *p, const uint8_t *s, const float *) {
+        uint32_t w[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) w[j] = (uint32_t)s[4 * j] | ((uint32_t)s[4 * j + 1] << 8) | ((uint32_t)s[4 * j + 2] << 16) | ((uint32_t)s[4 * j + 3] << 24);
+        *reinterpret_cast<uint4 *>(p) = make_uint4(w[0], w[1], w[2], w[3]);
     }
 };
 
+// One CTA per output row (b, y): the source pixels are gathered into shared memory (each thread fetches whole RGB pixels through
+// the x-table; the y-table lookup and the image metadata are read once per row), then the row is written out with aligned
+// vector stores -- head / body / tail, because a 897-element row starts at an arbitrary alignment.
 template <typename TOut>
-__global__ void k_resize(const uint8_t *__restrict__ src, const ImgMeta *__restrict__ meta,
-                         const int32_t *__restrict__ xtab, const int32_t *__restrict__ ytab, int B, int S,
-                         TOut *__restrict__ out) {
-    const long long per_img = (long long)S * S * 3;
-    const long long total = per_img * B;
-    long long g = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
-    if (g >= total) return;
-    const int row_el = S * 3;
-    int b = (int)(g / per_img);
-    int r = (int)(g - (long long)b * per_img);
-    int y = r / row_el;
-    int j = r - y * row_el;
-    int x = j / 3, c = j - x * 3;
-    TOut v[4];
-#pragma unroll
-    for (int e = 0; e < 4; ++e) {
-        if (g + e < total) {
-            const ImgMeta mt = meta[b];
-            const uint8_t *p = src + mt.offset + (long long)ytab[(size_t)b * S + y] * mt.pitch +
-                               (long long)xtab[(size_t)b * S + x] * 3 + c;
-            v[e] = PxOut<TOut>::cvt(__ldg(p));
-        } else {
-            v[e] = TOut(0);
-        }
-        if (++c == 3) { c = 0; if (++x == S) { x = 0; if (++y == S) { y = 0; ++b; } } }
+__global__ void __launch_bounds__(128)
+k_resize(const uint8_t *__restrict__ src, const ImgMeta *__restrict__ meta, const int32_t *__restrict__ xtab,
+         const int32_t *__restrict__ ytab, int B, int S, TOut *__restrict__ out) {
+    extern __shared__ uint8_t rowbuf[];  // S*3 bytes (+ 256-entry float LUT for TOut = float)
+    const int b = blockIdx.y, y = blockIdx.x;
+    const int n = S * 3;
+    float *lut = reinterpret_cast<float *>(rowbuf + ((n + 15) & ~15));
+    if (sizeof(TOut) == 4)
+        for (int i = threadIdx.x; i < 256; i += blockDim.x) lut[i] = scale_px((uint8_t)i);
+    const ImgMeta mt = meta[b];
+    const uint8_t *srow = src + mt.offset + (long long)ytab[(size_t)b * S + y] * mt.pitch;
+    const int32_t *xt = xtab + (size_t)b * S;
+    for (int x = threadIdx.x; x < S; x += blockDim.x) {
+        const uint8_t *p = srow + (long long)xt[x] * 3;
+        rowbuf[3 * x + 0] = __ldg(p);
+        rowbuf[3 * x + 1] = __ldg(p + 1);
+        rowbuf[3 * x + 2] = __ldg(p + 2);
     }
-    if (g + 4 <= total) {
-        PxOut<TOut>::st4(out + g, v[0], v[1], v[2], v[3]);
-    } else {
-        for (int e = 0; g + e < total; ++e) out[g + e] = v[e];
+    __syncthreads();
+    TOut *orow = out + ((size_t)b * S + y) * n;
+    constexpr int VEC = 16 / sizeof(TOut);  // elements per 16-byte store
+    const int mis = (int)((reinterpret_cast<uintptr_t>(orow) / sizeof(TOut)) % VEC);
+    const int head = mis ? min(VEC - mis, n) : 0;
+    for (int i = threadIdx.x; i < head; i += blockDim.x) orow[i] = PxOut<TOut>::cvt1(rowbuf[i], lut);
+    const int nvec = (n - head) / VEC;
+    for (int v = threadIdx.x; v < nvec; v += blockDim.x) {
+        const int i = head + v * VEC;
+        PxOut<TOut>::st16(orow + i, rowbuf + i, lut);
     }
+    for (int i = head + nvec * VEC + threadIdx.x; i < n; i += blockDim.x) orow[i] = PxOut<TOut>::cvt1(rowbuf[i], lut);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -122,19 +126,26 @@ k_conv1(const TIn *__restrict__ in, const float *__restrict__ w /*[27][32]*/, co
     for (int ky = 0; ky < 3; ++ky)
 #pragma unroll
         for (int kk = 0; kk < 9; ++kk) v[ky * 9 + kk] = InPx<TIn>::get(base + (long long)ky * S * 3 + kk, lut);
-    float4 acc[8];
+    // packed fp32 FMAs (fma.rn.f32x2): 16 per input value instead of 32 scalar ones -- this kernel is FMA-issue bound
+    float2 acc[16];
 #pragma unroll
-    for (int c = 0; c < 8; ++c) acc[c] = *reinterpret_cast<const float4 *>(&bs[c * 4]);
+    for (int c = 0; c < 16; ++c) acc[c] = *reinterpret_cast<const float2 *>(&bs[c * 2]);
 #pragma unroll
     for (int k = 0; k < 27; ++k) {
         const float4 *wp = reinterpret_cast<const float4 *>(&ws[k * 32]);
-        const float4 a = make_float4(v[k], v[k], v[k], v[k]);
+        const float2 a = make_float2(v[k], v[k]);
 #pragma unroll
-        for (int c = 0; c < 8; ++c) acc[c] = fma4(a, wp[c], acc[c]);
+        for (int c = 0; c < 8; ++c) {
+            const float4 w4 = wp[c];
+            acc[2 * c] = ffma2(a, make_float2(w4.x, w4.y), acc[2 * c]);
+            acc[2 * c + 1] = ffma2(a, make_float2(w4.z, w4.w), acc[2 * c + 1]);
+        }
     }
     T *o = out + pix * 32;
 #pragma unroll
-    for (int c = 0; c < 4; ++c) st8<T>(o + c * 8, relu4(acc[2 * c]), relu4(acc[2 * c + 1]));
+    for (int c = 0; c < 4; ++c)
+        st8<T>(o + c * 8, relu4(make_float4(acc[4 * c].x, acc[4 * c].y, acc[4 * c + 1].x, acc[4 * c + 1].y)),
+               relu4(make_float4(acc[4 * c + 2].x, acc[4 * c + 2].y, acc[4 * c + 3].x, acc[4 * c + 3].y)));
 }
 
 // ---------------------------------------------------------------------------------------------------
