@@ -90,6 +90,15 @@ int kdl_predict_u8_host(KdlModel *m, const uint8_t *h_src, size_t total_bytes, c
                         const int32_t *h, const int32_t *w, const int64_t *pitch, int32_t B,
                         float *h_dense_7);
 
+/* Pipelined form of kdl_predict_u8_host for throughput: returns as soon as the work is queued; up to two submits may be in
+ * flight, so the host->device copy of call i+1 (own copy stream, double-buffered staging) overlaps the kernels of call i.
+ * h_src and h_dense_7 should be pinned and must stay valid until the matching kdl_wait, which retires the OLDEST submit.
+ * A third submit waits for the oldest one itself.  No reference counterpart (the reference gateway is strictly one request
+ * at a time, gateway.dockerfile:17). */
+int kdl_submit_u8_host(KdlModel *m, const uint8_t *h_src, size_t total_bytes, const int64_t *offset,
+                       const int32_t *h, const int32_t *w, const int64_t *pitch, int32_t B, float *h_dense_7);
+int kdl_wait(KdlModel *m);
+
 /* Same as kdl_forward but from/to HOST memory (the PredictRequest tensor_content / PredictResponse
  * float_val payloads of model_server.py:35-36,46-47). */
 int kdl_forward_host(KdlModel *m, const float *h_input_8, int32_t B, float *h_dense_7);

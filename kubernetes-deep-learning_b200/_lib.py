@@ -16,7 +16,7 @@ SYMBOLS = [
     "kdl_create", "kdl_destroy", "kdl_last_error", "kdl_weight_count", "kdl_load_weights",
     "kdl_preprocess_u8", "kdl_forward", "kdl_predict_u8", "kdl_predict_u8_host", "kdl_forward_host",
     "kdl_num_taps", "kdl_tap_name", "kdl_layer_output", "kdl_last_launch_count", "kdl_gemm_bf16",
-    "kdl_version", "kdl_profile_begin", "kdl_profile_end", "kdl_preprocess_u8_static",
+    "kdl_version", "kdl_profile_begin", "kdl_profile_end", "kdl_preprocess_u8_static", "kdl_submit_u8_host", "kdl_wait",
 ]
 STATIC_MAX_BATCH, STATIC_MAX_SIZE = 32, 512
 
@@ -63,6 +63,8 @@ def load():
     lib.kdl_predict_u8.argtypes = [P, P, P, P, P, P, c_int32, P, P]
     lib.kdl_predict_u8_host.argtypes = [P, P, c_size_t, P, P, P, P, c_int32, P]
     lib.kdl_forward_host.argtypes = [P, P, c_int32, P]
+    lib.kdl_submit_u8_host.argtypes = [P, P, c_size_t, P, P, P, P, c_int32, P]
+    lib.kdl_wait.argtypes = [P]
     lib.kdl_num_taps.argtypes = [P]
     lib.kdl_tap_name.argtypes = [P, c_int32]
     lib.kdl_tap_name.restype = c_char_p

@@ -129,6 +129,14 @@ struct KdlModel {
     cudaEvent_t slot_ev[NSLOT];
     int slot = 0;
     cudaStream_t own_stream = nullptr;
+    // pipelined host path (kdl_submit_u8_host / kdl_wait): H2D of call i+1 on copy_stream overlaps the kernels of call i
+    cudaStream_t copy_stream = nullptr;
+    uint8_t *pipe_src[2] = {nullptr, nullptr};
+    size_t pipe_cap[2] = {0, 0};
+    float *pipe_logits[2] = {nullptr, nullptr};
+    cudaEvent_t pipe_copied[2], pipe_done[2];
+    bool pipe_init = false;
+    int pipe_head = 0, pipe_inflight = 0;
 
     // TMA descriptors of the activation buffers viewed as [rows, K] matrices are built per call site
     std::vector<Tap> taps;
@@ -719,6 +727,15 @@ extern "C" int kdl_destroy(KdlModel *m) {
     if (m->own_stream) cudaStreamDestroy(m->own_stream);
     for (cudaEvent_t e : m->ev_pool) cudaEventDestroy(e);
     for (auto &g : m->graphs) if (g.exec) cudaGraphExecDestroy(g.exec);
+    if (m->pipe_init) {
+        for (int i = 0; i < 2; ++i) {
+            if (m->pipe_src[i]) cudaFree(m->pipe_src[i]);
+            if (m->pipe_logits[i]) cudaFree(m->pipe_logits[i]);
+            cudaEventDestroy(m->pipe_copied[i]);
+            cudaEventDestroy(m->pipe_done[i]);
+        }
+        cudaStreamDestroy(m->copy_stream);
+    }
     delete m;
     return KDL_OK;
 }
@@ -891,6 +908,55 @@ extern "C" int kdl_predict_u8_host(KdlModel *m, const uint8_t *h_src, size_t tot
     if (rc) return rc;
     CK(cudaMemcpyAsync(h_dense_7, m->d_logits, (size_t)B * 10 * 4, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
+    return KDL_OK;
+}
+
+extern "C" int kdl_wait(KdlModel *m) {
+    if (!m) { set_err(g_err, "kdl_wait: null model"); return KDL_EINVAL; }
+    char *err = m->err;
+    if (m->pipe_inflight == 0) return KDL_OK;
+    CK(cudaSetDevice(m->cfg.device));
+    const int slot = (m->pipe_head - m->pipe_inflight + 4) & 1;  // oldest in-flight submit
+    CK(cudaEventSynchronize(m->pipe_done[slot]));
+    m->pipe_inflight--;
+    return KDL_OK;
+}
+
+extern "C" int kdl_submit_u8_host(KdlModel *m, const uint8_t *h_src, size_t total_bytes, const int64_t *offset, const int32_t *h,
+                                  const int32_t *w, const int64_t *pitch, int32_t B, float *h_dense_7) {
+    int rc = check_call(m, B, true);
+    if (rc) return rc;
+    char *err = m->err;
+    if (!h_src || !h_dense_7 || total_bytes == 0) { set_err(err, "kdl_submit_u8_host: null buffer"); return KDL_EINVAL; }
+    if (!m->pipe_init) {
+        CK(cudaStreamCreateWithFlags(&m->copy_stream, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; ++i) {
+            CK(cudaEventCreateWithFlags(&m->pipe_copied[i], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&m->pipe_done[i], cudaEventDisableTiming));
+            CK(cudaMalloc((void **)&m->pipe_logits[i], (size_t)m->cfg.max_batch * 10 * sizeof(float)));
+        }
+        m->pipe_init = true;
+    }
+    if (m->pipe_inflight == 2) { if ((rc = kdl_wait(m))) return rc; }  // both staging buffers busy: retire the oldest
+    const int slot = m->pipe_head & 1;
+    if (total_bytes > m->pipe_cap[slot]) {
+        CK(cudaStreamSynchronize(m->own_stream));
+        if (m->pipe_src[slot]) CK(cudaFree(m->pipe_src[slot]));
+        m->pipe_src[slot] = nullptr; m->pipe_cap[slot] = 0;
+        size_t cap = total_bytes + total_bytes / 4;
+        CK(cudaMalloc((void **)&m->pipe_src[slot], cap));
+        m->pipe_cap[slot] = cap;
+    }
+    // the staging buffer of this slot was last read by the submit two calls ago, which has been retired above
+    CK(cudaMemcpyAsync(m->pipe_src[slot], h_src, total_bytes, cudaMemcpyHostToDevice, m->copy_stream));
+    CK(cudaEventRecord(m->pipe_copied[slot], m->copy_stream));
+    CK(cudaStreamWaitEvent(m->own_stream, m->pipe_copied[slot], 0));
+    rc = kdl_predict_u8(m, m->pipe_src[slot], offset, h, w, pitch, B, m->pipe_logits[slot], m->own_stream);
+    if (rc) return rc;
+    CK(cudaMemcpyAsync(h_dense_7, m->pipe_logits[slot], (size_t)B * 10 * sizeof(float), cudaMemcpyDeviceToHost, m->own_stream));
+    CK(cudaEventRecord(m->pipe_done[slot], m->own_stream));
+    m->pipe_head++;
+    m->pipe_inflight++;
     return KDL_OK;
 }
 

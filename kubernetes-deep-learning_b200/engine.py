@@ -164,6 +164,17 @@ class Model:
                                                 out.ctypes.data), self.h)
         return out
 
+    def submit_packed_host(self, pk: PackedImages, out: torch.Tensor) -> None:
+        """Pipelined end-to-end call: queues H2D + kernels + D2H and returns; `out` is a pinned float32 CPU tensor (B,10) that
+        is valid after the matching `wait()`.  At most two submits are in flight (the copy of one overlaps the kernels of the other)."""
+        assert out.dtype == torch.float32 and not out.is_cuda and out.numel() >= pk.B * 10
+        _lib.check(self.lib.kdl_submit_u8_host(self.h, pk.host.data_ptr(), pk.total_bytes, *pk.meta_ptrs(), pk.B,
+                                               out.data_ptr()), self.h)
+
+    def wait(self) -> None:
+        """Retires the oldest in-flight `submit_packed_host`."""
+        _lib.check(self.lib.kdl_wait(self.h), self.h)
+
     def predict_uint8(self, images: Sequence[np.ndarray]) -> np.ndarray:
         outs = []
         for i in range(0, len(images), self.max_batch):
