@@ -19,6 +19,7 @@
 #include "conv_tc.cuh"
 #include "dw_tma.cuh"
 #include "pool_tma.cuh"
+#include "sepconv_tc.cuh"
 #include "kernels.cuh"
 
 using namespace kdl;
@@ -98,6 +99,7 @@ struct KdlModel {
     KdlConfig cfg;
     char err[512];
     bool weights_loaded = false;
+    bool no_fused_sepconv = false;   // KDL_NO_FUSED_SEPCONV=1: separate depthwise + pointwise kernels everywhere (A/B)
     int microbatch_mb = 0;           // KDL_MICROBATCH_MB: size (MiB) of the L2-resident depthwise->pointwise hand-off, 0 = off
     bool conv_shifted_taps = false;  // KDL_CONV2_TAPS=1: 9 shifted TMA boxes per tile instead of the staged halo (A/B)
     bool use_2cta = false;    // KDL_GEMM_2CTA=1: CTA-pair (cta_group::2) kernel for the K>=512 layers (A/B measurements)
@@ -156,9 +158,10 @@ struct KdlModel {
     int cls_launches[16];
 };
 
-enum ProfClass { PC_RESIZE = 0, PC_CONV1, PC_CONV2, PC_DW, PC_PW_TC_HBM, PC_PW_TC_TENSOR, PC_GEMM_SIMPLE, PC_SUBSAMPLE, PC_POOL, PC_HEAD, PC_COUNT };
+enum ProfClass { PC_RESIZE = 0, PC_CONV1, PC_CONV2, PC_DW, PC_PW_TC_HBM, PC_PW_TC_TENSOR, PC_GEMM_SIMPLE, PC_SUBSAMPLE, PC_POOL, PC_HEAD, PC_SEPFUSED, PC_COUNT };
 static const char *PROF_NAMES[PC_COUNT] = {"k_resize", "k_conv1", "conv2_implicit_gemm", "k_dw3x3", "k_gemm_tc[K<=256,hbm-bound]",
-                                           "k_gemm_tc[K>=728,tensor-bound]", "k_gemm_simple", "k_subsample2", "k_maxpool_add", "k_gap_head"};
+                                           "k_gemm_tc[K>=728,tensor-bound]", "k_gemm_simple", "k_subsample2", "k_maxpool_add", "k_gap_head",
+                                           "k_sepconv_tc[fused dw+pw,hbm-bound]"};
 
 static cudaEvent_t prof_event(KdlModel *m) {
     if (m->ev_used == m->ev_pool.size()) {
@@ -325,6 +328,21 @@ template <typename T> struct Runner {
         return KDL_OK;
     }
 
+    bool can_fuse(int si) const { return use_tc() && !m->no_fused_sepconv && sepc::supported(m->pw[si].K, m->pw[si].N); }
+    // fused depthwise+pointwise (sepconv_tc.cuh); in and out must be different buffers (tiles read a halo)
+    int sepconv_fused(const T *in, int si, T *out, int H, int relu_in, int relu_out) {
+        const GemmW &g = m->pw[si];
+        const double px = (double)B * H * H;
+        prof_open(m, st, PC_SEPFUSED, 2.0 * px * (9.0 * g.K + (double)g.K * g.N), (px * g.K + px * g.N + (double)g.K * g.N) * 2.0 + 36.0 * g.K,
+                  "sepfused H=%d K=%d N=%d", H, g.K, g.N);
+        int rc = sepc::launch(m->tma, (const bf16 *)in, m->dwpad[si], &g.tmB, g.bias, (bf16 *)out, B, H, H, g.K, g.N, ld(g.K), ld(g.N),
+                              relu_in, relu_out, st, m->err);
+        prof_close(m, st);
+        if (rc != KDL_OK) return rc;
+        m->launches++;
+        return KDL_OK;
+    }
+
     // Conv2D(1x1, strides 2, 'same') + BN : residual projection.  in: [B,H,H,Cin] -> out [B,Ho,Ho,Cout]
     int projection(const T *in, const GemmW &g, T *out, int H, int Ho, bool have_sub = false) {
         int M = B * Ho * Ho;
@@ -403,19 +421,25 @@ template <typename T> struct Runner {
             snprintf(name, sizeof name, "block%d_res_bn", blk);
             RUN(tap(name, R, Ho, rg.N, 0));
             // sepconv1: ReLU on load except block2 (input is already post-ReLU there)
-            RUN(sepconv(X, si, U, H, blk != 2, 1));  // next sepconv's ReLU folded into this GEMM's epilogue
+            if (can_fuse(si)) RUN(sepconv_fused(X, si, U, H, blk != 2, 1));
+            else RUN(sepconv(X, si, U, H, blk != 2, 1));  // next sepconv's ReLU folded into this GEMM's epilogue
             snprintf(name, sizeof name, "block%d_sepconv1_bn", blk);
             RUN(tap(name, U, H, m->pw[si].N, 1));
             ++si;
-            // in-place U -> T -> U is fine per micro-batch: the GEMM of micro-batch i only overwrites U rows already consumed
-            RUN(sepconv(U, si, U, H, 0, 0));
+            T *V = U;  // where sepconv2's output lives
+            if (can_fuse(si)) {
+                V = Tb;  // the fused kernel cannot run in place, and T is free when nothing is written between dw and pw
+                RUN(sepconv_fused(U, si, V, H, 0, 0));
+            } else {
+                RUN(sepconv(U, si, U, H, 0, 0));
+            }
             snprintf(name, sizeof name, "block%d_sepconv2_bn", blk);
-            RUN(tap(name, U, H, m->pw[si].N, 0));
+            RUN(tap(name, V, H, m->pw[si].N, 0));
             int C = m->pw[si].N;
             ++si;
             // blocks 2 and 3 feed another strided projection: let the pool kernel emit its input (tensor-core path only)
             const bool emit_sub = use_tc() && (blk == 2 || blk == 3);
-            RUN(pool_add(U, R, X, emit_sub ? (T *)m->S : nullptr, H, C, Ho));
+            RUN(pool_add(V, R, X, emit_sub ? (T *)m->S : nullptr, H, C, Ho));
             have_sub = emit_sub;
             snprintf(name, sizeof name, "block%d_out", blk);
             RUN(tap(name, X, Ho, C, 0));
@@ -709,7 +733,8 @@ extern "C" int kdl_create(const KdlConfig *cfg, KdlModel **out) {
     { const char *e1 = getenv("KDL_GEMM_2CTA"); m->use_2cta = e1 && e1[0] == '1'; }
     { const char *e1 = getenv("KDL_CONV2_TAPS"); m->conv_shifted_taps = e1 && e1[0] == '1'; }
     { const char *e1 = getenv("KDL_MICROBATCH_MB"); m->microbatch_mb = e1 ? atoi(e1) : 0; }
-    if ((rc = tc::configure(m->err)) != KDL_OK || (rc = tc2::configure2(m->err)) != KDL_OK || (rc = convtc::configure(m->err)) != KDL_OK || (rc = dwt::configure(m->err)) != KDL_OK || (rc = poolt::configure(m->err)) != KDL_OK) { set_err(g_err, "%s", m->err); kdl_destroy(m); return rc; }
+    { const char *e1 = getenv("KDL_NO_FUSED_SEPCONV"); m->no_fused_sepconv = e1 && e1[0] == '1'; }
+    if ((rc = tc::configure(m->err)) != KDL_OK || (rc = tc2::configure2(m->err)) != KDL_OK || (rc = convtc::configure(m->err)) != KDL_OK || (rc = dwt::configure(m->err)) != KDL_OK || (rc = poolt::configure(m->err)) != KDL_OK || (rc = sepc::configure(m->err)) != KDL_OK) { set_err(g_err, "%s", m->err); kdl_destroy(m); return rc; }
     *out = m;
     return KDL_OK;
 }
