@@ -100,3 +100,54 @@ def test_replica_set_matches_single_model():
     finally:
         rs.close()
     np.testing.assert_array_equal(got, want)
+
+
+def test_unmodified_gateway_flow_over_grpc_and_http(gw, tmp_path):
+    """End to end through both shells of SURVEY.md §8f: HTTP POST /predict -> apply_model (file:// URL) -> engine, and the
+    model_server.py call sequence against the PredictionService stand-in over a real gRPC channel."""
+    import json
+    import threading
+    import urllib.request
+    grpc = pytest.importorskip("grpc")
+    from PIL import Image
+    from kdl_b200 import gateway, http_gateway, serving
+    from oracle import preprocess_oracle as po
+    from oracle import xception_oracle as xo
+    g, W = gw
+    rng = np.random.default_rng(8)
+    img = rng.integers(0, 256, (333, 444, 3), dtype=np.uint8)
+    path = tmp_path / "pic.png"
+    Image.fromarray(img).save(path)
+    want = xo.forward(W, po.preprocess_pillow(img), torch.float64)[0]
+
+    # --- gRPC: what model_server.py does with TF_SERVING_HOST pointing at this server
+    server, port = serving.make_server(g.model.serving_default, "127.0.0.1:0")
+    server.start()
+    try:
+        channel = grpc.insecure_channel(f"127.0.0.1:{port}", options=[("grpc.max_send_message_length", 64 << 20)])
+        stub = serving.PredictionServiceStub(channel)
+        X = g.preprocessor.from_path(str(path))
+        pb_request = serving.PredictRequest()
+        pb_request.model_spec.name = 'clothing-model'
+        pb_request.model_spec.signature_name = 'serving_default'
+        pb_request.inputs['input_8'].CopyFrom(serving.make_tensor_proto(X, shape=X.shape))
+        pb_result = stub.Predict(pb_request, timeout=20.0)
+        pred = np.array(pb_result.outputs['dense_7'].float_val)
+        assert rel(pred, want) <= 2e-2 and pred.argmax() == want.argmax()
+        channel.close()
+    finally:
+        server.stop(0)
+
+    # --- HTTP: POST /predict {"url": ...}
+    srv = http_gateway.make_http_server(g.apply_model, "127.0.0.1", 0)
+    threading.Thread(target=srv.serve_forever, daemon=True).start()
+    try:
+        req = urllib.request.Request(f"http://127.0.0.1:{srv.server_address[1]}/predict",
+                                     data=json.dumps({"url": path.as_uri()}).encode(), headers={"Content-Type": "application/json"})
+        with urllib.request.urlopen(req, timeout=30) as r:
+            body = json.loads(r.read())
+        assert list(body) == gateway.labels
+        got = np.array(list(body.values()))
+        np.testing.assert_allclose(got, pred, rtol=0, atol=0)          # same engine, same logits as the gRPC path
+    finally:
+        srv.shutdown()
