@@ -283,7 +283,13 @@ def main():
                 "unit": "TFLOP/s"}
     else:
         roof = {"bound": "hbm", "achieved": dom["achieved_gbs"], "peak": peaks["hbm_gbs"], "unit": "GB/s"}
-    roof.update({"frac": roof["achieved"] / roof["peak"], "traffic": None, "kernel": dom["kernel"],
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if os.path.exists(tpath):
+        tj = json.load(open(tpath))
+        if dom["kernel"] in tj:
+            traffic = dict(tj[dom["kernel"]], source=tj.get("_source"))
+    roof.update({"frac": roof["achieved"] / roof["peak"], "traffic": traffic, "kernel": dom["kernel"],
                  "launches_per_step": dom["launches_per_step"], "avg_launch_ms": dom["ms_per_step"] / max(dom["launches_per_step"], 1),
                  "peak_source": peaks["_source"] + (" sustained bf16" if dom["bound"] == "tensor" else " copy bandwidth"),
                  "timing": f"cuda events around each launch over {K} steps (separate pass right after the timed region)"})
