@@ -130,8 +130,8 @@ int kdl_last_launch_count(const KdlModel *m);
 
 /* Stand-alone pointwise GEMM entry (kernel-level parity and roofline measurement):
  * out[M,N] = act( A[M,K] * W[K,N] + bias[N] ) (+ residual[M,N]); bf16 device buffers, W given K-major
- * as Wt[N,K]; residual may be NULL.  `relu` bit 0 = apply ReLU; bit 1 = force the single-CTA tcgen05 kernel (default: the
- * CTA-pair cta_group::2 kernel when M >= 256). */
+ * as Wt[N,K]; residual may be NULL.  `relu` bit 0 = apply ReLU; bit 1 = force the single-CTA 128x256 tcgen05 kernel (default: the
+ * CTA-pair cta_group::2 kernel when M >= 256); bit 2 = the 256x256-per-CTA kernel. */
 int kdl_gemm_bf16(const void *d_A, const void *d_Wt, const float *d_bias, const void *d_residual,
                   void *d_out, int32_t M, int32_t N, int32_t K, int32_t relu, void *stream);
 

@@ -16,6 +16,7 @@
 #include "../../include/kdl.h"
 #include "gemm_tc.cuh"
 #include "gemm_tc2.cuh"
+#include "gemm_tc_m2.cuh"
 #include "conv_tc.cuh"
 #include "dw_tma.cuh"
 #include "pool_tma.cuh"
@@ -102,7 +103,7 @@ struct KdlModel {
     bool no_fused_sepconv = false;   // KDL_NO_FUSED_SEPCONV=1: separate depthwise + pointwise kernels everywhere (A/B)
     int microbatch_mb = 0;           // KDL_MICROBATCH_MB: size (MiB) of the L2-resident depthwise->pointwise hand-off, 0 = off
     bool conv_shifted_taps = false;  // KDL_CONV2_TAPS=1: 9 shifted TMA boxes per tile instead of the staged halo (A/B)
-    bool use_2cta = false;    // KDL_GEMM_2CTA=1: CTA-pair (cta_group::2) kernel for the K>=512 layers (A/B measurements)
+    int gemm_variant = 1;     // KDL_GEMM_VARIANT: tensor-bound layers use 1 = 128x256 single CTA, 2 = CTA pair (cta_group::2), 3 = 256x256 per CTA
     int launches = 0;
     int last_B = 0;
     int sp[7];  // spatial chain S,H1..H6
@@ -285,7 +286,10 @@ template <typename T> struct Runner {
         if (use_tc() && rm.mode == 0 && tc::shape_supported(M, g.N, g.K)) {
             prof_open(m, st, g.K >= 512 ? PC_PW_TC_TENSOR : PC_PW_TC_HBM, flops, bytes, "gemm M=%d N=%d K=%d", M, g.N, g.K);
             int rc;
-            if (m->use_2cta && M >= 2048 && g.K >= 512)  // opt-in (KDL_GEMM_2CTA=1): with 128-byte aligned rows the single-CTA kernel is faster
+            if (m->gemm_variant == 3 && M >= 2048 && g.K >= 512)  // 256x256 tile per CTA (two M tiles share each weight block)
+                rc = tcm2::launch(m->tma, (const bf16 *)A, &g.tmB, g.bias, (const bf16 *)resid, (bf16 *)out, M, g.N, g.K, relu, st, m->err,
+                                  ld(g.K), ld(g.N));
+            else if (m->gemm_variant == 2 && M >= 2048 && g.K >= 512)  // CTA pair (cta_group::2)
                 rc = tc2::launch_gemm2(m->tma, (const bf16 *)A, &g.tmB2, g.bias, (const bf16 *)resid, (bf16 *)out, M, g.N, g.K, relu,
                                        st, m->err, ld(g.K), ld(g.N));
             else
@@ -730,11 +734,11 @@ extern "C" int kdl_create(const KdlConfig *cfg, KdlModel **out) {
     CK(cudaStreamCreateWithFlags(&m->own_stream, cudaStreamNonBlocking));
     CK(cudaFuncSetAttribute(k_gap_head<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
     CK(cudaFuncSetAttribute(k_gap_head<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
-    { const char *e1 = getenv("KDL_GEMM_2CTA"); m->use_2cta = e1 && e1[0] == '1'; }
+    { const char *e1 = getenv("KDL_GEMM_VARIANT"); m->gemm_variant = e1 ? atoi(e1) : 1; }
     { const char *e1 = getenv("KDL_CONV2_TAPS"); m->conv_shifted_taps = e1 && e1[0] == '1'; }
     { const char *e1 = getenv("KDL_MICROBATCH_MB"); m->microbatch_mb = e1 ? atoi(e1) : 0; }
     { const char *e1 = getenv("KDL_NO_FUSED_SEPCONV"); m->no_fused_sepconv = e1 && e1[0] == '1'; }
-    if ((rc = tc::configure(m->err)) != KDL_OK || (rc = tc2::configure2(m->err)) != KDL_OK || (rc = convtc::configure(m->err)) != KDL_OK || (rc = dwt::configure(m->err)) != KDL_OK || (rc = poolt::configure(m->err)) != KDL_OK || (rc = sepc::configure(m->err)) != KDL_OK) { set_err(g_err, "%s", m->err); kdl_destroy(m); return rc; }
+    if ((rc = tc::configure(m->err)) != KDL_OK || (rc = tc2::configure2(m->err)) != KDL_OK || (rc = tcm2::configure(m->err)) != KDL_OK || (rc = convtc::configure(m->err)) != KDL_OK || (rc = dwt::configure(m->err)) != KDL_OK || (rc = poolt::configure(m->err)) != KDL_OK || (rc = sepc::configure(m->err)) != KDL_OK) { set_err(g_err, "%s", m->err); kdl_destroy(m); return rc; }
     *out = m;
     return KDL_OK;
 }
@@ -1051,6 +1055,16 @@ extern "C" int kdl_gemm_bf16(const void *d_A, const void *d_Wt, const float *d_b
         return KDL_ECUDA;
     }
     (void)err;
+    if ((relu >> 2) & 1) {
+        if ((rc = tcm2::configure(g_err))) return rc;
+        CUtensorMap tmB256;
+        if (!enc.encode_2d(&tmB256, d_Wt, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, tc::BLOCK_K, tc::BLOCK_N, 128)) {
+            set_err(g_err, "kdl_gemm_bf16: tensor map encode failed");
+            return KDL_ECUDA;
+        }
+        return tcm2::launch(enc, (const bf16 *)d_A, &tmB256, d_bias, (const bf16 *)d_residual, (bf16 *)d_out, M, N, K, relu & 1,
+                            (cudaStream_t)stream, g_err);
+    }
     if (one_cta)
         return tc::launch_gemm(enc, (const bf16 *)d_A, &tmB, d_bias, (const bf16 *)d_residual, (bf16 *)d_out, M, N, K, relu & 1,
                                (cudaStream_t)stream, g_err);

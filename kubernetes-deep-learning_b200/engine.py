@@ -211,7 +211,7 @@ class Model:
 
 
 def gemm_bf16(A: torch.Tensor, Wt: torch.Tensor, bias: torch.Tensor, residual: Optional[torch.Tensor] = None,
-              relu: bool = False, out: Optional[torch.Tensor] = None, one_cta: bool = False) -> torch.Tensor:
+              relu: bool = False, out: Optional[torch.Tensor] = None, one_cta: bool = False, m256: bool = False) -> torch.Tensor:
     """Stand-alone tcgen05 GEMM: act(A[M,K] @ Wt[N,K]^T + bias) (+ residual); bf16 CUDA tensors.
     one_cta=True forces the single-CTA kernel; default is the CTA-pair (cta_group::2) kernel when M >= 256."""
     lib = _lib.load()
@@ -225,5 +225,5 @@ def gemm_bf16(A: torch.Tensor, Wt: torch.Tensor, bias: torch.Tensor, residual: O
     with torch.cuda.device(A.device):
         _lib.check(lib.kdl_gemm_bf16(A.data_ptr(), Wt.data_ptr(), bias.data_ptr(),
                                      residual.data_ptr() if residual is not None else None, out.data_ptr(), M, N, K,
-                                     int(relu) | (2 if one_cta else 0), st))
+                                     int(relu) | (2 if one_cta else 0) | (4 if m256 else 0), st))
     return out

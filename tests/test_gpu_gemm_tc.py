@@ -17,7 +17,7 @@ SHAPES = [
 
 @pytest.mark.parametrize("M,N,K", SHAPES)
 @pytest.mark.parametrize("relu,resid", [(False, False), (True, False), (False, True)])
-@pytest.mark.parametrize("one_cta", [True, False], ids=["cta1", "cta2"])
+@pytest.mark.parametrize("one_cta", [True, False, "m256"], ids=["cta1", "cta2", "m256"])
 def test_gemm_tc_matches_fp32_reference(M, N, K, relu, resid, one_cta):
     import kdl_b200  # noqa: F401
     from kdl_b200 import engine
@@ -26,7 +26,7 @@ def test_gemm_tc_matches_fp32_reference(M, N, K, relu, resid, one_cta):
     Wt = (torch.randn((N, K), generator=g, device="cuda") / K ** 0.5).to(torch.bfloat16)
     bias = torch.randn((N,), generator=g, device="cuda")
     R = torch.randn((M, N), generator=g, device="cuda").to(torch.bfloat16) if resid else None
-    out = engine.gemm_bf16(A, Wt, bias, R, relu, one_cta=one_cta)
+    out = engine.gemm_bf16(A, Wt, bias, R, relu, one_cta=one_cta is True, m256=one_cta == "m256")
     torch.cuda.synchronize()
     ref = A.float() @ Wt.float().t() + bias
     if relu:
@@ -37,7 +37,7 @@ def test_gemm_tc_matches_fp32_reference(M, N, K, relu, resid, one_cta):
     assert err <= 1e-2, err
 
 
-@pytest.mark.parametrize("one_cta", [True, False], ids=["cta1", "cta2"])
+@pytest.mark.parametrize("one_cta", [True, False, "m256"], ids=["cta1", "cta2", "m256"])
 def test_gemm_tc_in_place_residual(one_cta):
     import kdl_b200  # noqa: F401
     from kdl_b200 import engine
@@ -48,6 +48,6 @@ def test_gemm_tc_in_place_residual(one_cta):
     bias = torch.randn((N,), generator=g, device="cuda")
     X = torch.randn((M, N), generator=g, device="cuda").to(torch.bfloat16)
     ref = A.float() @ Wt.float().t() + bias + X.float()
-    engine.gemm_bf16(A, Wt, bias, X, False, out=X, one_cta=one_cta)     # the middle-flow skip connection is updated in place
+    engine.gemm_bf16(A, Wt, bias, X, False, out=X, one_cta=one_cta is True, m256=one_cta == "m256")     # the middle-flow skip connection is updated in place
     torch.cuda.synchronize()
     assert (X.float() - ref).abs().max().item() / ref.abs().max().item() <= 1e-2
