@@ -4,6 +4,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <utility>
+
 namespace kdl {
 
 typedef __nv_bfloat16 bf16;
@@ -69,6 +71,34 @@ template <> __device__ __forceinline__ float ld1<bf16>(const bf16 *p) { return _
 template <typename T> __device__ __forceinline__ void st1(T *p, float v);
 template <> __device__ __forceinline__ void st1<float>(float *p, float v) { *p = v; }
 template <> __device__ __forceinline__ void st1<bf16>(bf16 *p, float v) { *p = __float2bfloat16_rn(v); }
+
+// Programmatic dependent launch: a kernel launched with the PDL attribute may start while its predecessor in the stream is still
+// running; pdl_wait() blocks until the predecessor has completed and its writes are visible, pdl_launch_dependents() lets the
+// successor be scheduled early.  Both are no-ops for a normal launch.  Every kernel of the forward pass runs its prologue (barrier
+// init, TMEM allocation, descriptor prefetch), then pdl_wait(), then touches global memory -- so launch latency and prologues of
+// the ~80 kernels overlap their predecessors' tails, which is what batch-1 latency is made of.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+inline bool &pdl_enabled() {
+    static thread_local bool on = false;
+    return on;
+}
+// cudaLaunchKernelEx wrapper: same as kernel<<<grid, block, smem, st>>>(args...) plus the PDL attribute when enabled
+template <typename... Params, typename... Args>
+inline cudaError_t launch_k(void (*kernel)(Params...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args &&...args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, Params(std::forward<Args>(args))...);
+}
 
 // packed fp32 FMA (Blackwell FFMA2): d = a * b + c on two lanes
 __device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {

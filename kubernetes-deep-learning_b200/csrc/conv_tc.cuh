@@ -56,6 +56,8 @@ k_conv3x3_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     tc_fence_after();
     uint32_t tmem_base;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+    pdl_launch_dependents();
+    pdl_wait();
 
     if (warp == 0) {
         if (lane == 0) {
@@ -165,7 +167,8 @@ inline int launch(const TmaEncoder &enc, const bf16 *in, const CUtensorMap *tmB,
     }
     const int tiles = (M + BLOCK_M - 1) / BLOCK_M;
     const int grid = tiles < num_sms() ? tiles : num_sms();
-    k_conv3x3_tc<<<grid, NUM_THREADS, SMEM_BYTES, st>>>(tmA, *tmB, bias, out, M, relu, ConvGeom{Hin, Win, Hin - 2, Win - 2}, box_rows);
+    launch_k(k_conv3x3_tc, dim3(grid), dim3(NUM_THREADS), SMEM_BYTES, st, tmA, *tmB, bias, out, M, relu, ConvGeom{Hin, Win, Hin - 2, Win - 2},
+             box_rows);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         snprintf(err, 512, "k_conv3x3_tc launch (B=%d H=%d): %s", B, Hin, cudaGetErrorString(e));

@@ -160,6 +160,8 @@ k_dw_tma(const __grid_constant__ CUtensorMap tmIn, const float *__restrict__ wpa
         tc::fence_barrier_init();
     }
     __syncthreads();
+    pdl_launch_dependents();
+    pdl_wait();
 
     if (warp == n_cwarps) {
         // ================= producer warp =================
@@ -297,8 +299,8 @@ inline int launch(const tc::TmaEncoder &enc, const bf16 *in, const float *wpad, 
     if (per_sm < 1) per_sm = 1;
     const int nsm = tc::num_sms() * per_sm;
     const int grid = p.total_tiles < nsm ? p.total_tiles : nsm;
-    if (relu_in) k_dw_tma<true><<<grid, p.consumer_threads + 32, smem_bytes(p), st>>>(tm, wpad, out, p);
-    else k_dw_tma<false><<<grid, p.consumer_threads + 32, smem_bytes(p), st>>>(tm, wpad, out, p);
+    if (relu_in) launch_k(k_dw_tma<true>, dim3(grid), dim3(p.consumer_threads + 32), smem_bytes(p), st, tm, wpad, out, p);
+    else launch_k(k_dw_tma<false>, dim3(grid), dim3(p.consumer_threads + 32), smem_bytes(p), st, tm, wpad, out, p);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         snprintf(err, 512, "k_dw_tma launch (B=%d H=%d C=%d threads=%d smem=%u): %s", B, H, C, p.consumer_threads + 32, smem_bytes(p),

@@ -102,6 +102,7 @@ struct KdlModel {
     bool weights_loaded = false;
     bool no_fused_sepconv = false;   // KDL_NO_FUSED_SEPCONV=1: separate depthwise + pointwise kernels everywhere (A/B)
     int microbatch_mb = 0;           // KDL_MICROBATCH_MB: size (MiB) of the L2-resident depthwise->pointwise hand-off, 0 = off
+    bool use_pdl = false;            // KDL_PDL=1 enables programmatic dependent launch (measured: -2 % batch-1 latency, no throughput gain)
     bool conv_shifted_taps = false;  // KDL_CONV2_TAPS=1: 9 shifted TMA boxes per tile instead of the staged halo (A/B)
     int gemm_variant = 1;     // KDL_GEMM_VARIANT: tensor-bound layers use 1 = 128x256 single CTA, 2 = CTA pair (cta_group::2), 3 = 256x256 per CTA
     int launches = 0;
@@ -354,7 +355,7 @@ template <typename T> struct Runner {
         if (use_tc() && tc::shape_supported(M, g.N, g.K)) {
             long long total = (long long)M * (g.K / 4);
             prof_open(m, st, PC_SUBSAMPLE, 0.0, 2.0 * M * g.K * sizeof(T));
-            k_subsample2<T><<<(unsigned)((total + 255) / 256), 256, 0, st>>>(in, (T *)m->S, B, H, H, g.K, ld(g.K), Ho, Ho);
+            launch_k(k_subsample2<T>, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, st, in, (T *)m->S, B, H, H, g.K, ld(g.K), Ho, Ho);
             prof_close(m, st);
             LAUNCH_CHECK();
             return gemm((const T *)m->S, g, nullptr, out, M, 0, RowMap{0, 0, 0, 0, 0, 0});
@@ -396,8 +397,8 @@ template <typename T> struct Runner {
             unsigned grid = (unsigned)((threads + 127) / 128);
             prof_open(m, st, PC_CONV1, 2.0 * 27 * 32 * B * sp[1] * sp[1],
                       (double)B * sp[0] * sp[0] * 3 * (in_f32 ? 4 : 1) + (double)B * sp[1] * sp[1] * 32 * sizeof(T));
-            if (in_f32) k_conv1<float, T><<<grid, 128, 0, st>>>(in_f32, m->w_conv1, m->b_conv1, U, B, sp[0], sp[1]);
-            else k_conv1<uint8_t, T><<<grid, 128, 0, st>>>(in_u8, m->w_conv1, m->b_conv1, U, B, sp[0], sp[1]);
+            if (in_f32) launch_k(k_conv1<float, T>, dim3(grid), dim3(128), 0, st, in_f32, m->w_conv1, m->b_conv1, U, B, sp[0], sp[1]);
+            else launch_k(k_conv1<uint8_t, T>, dim3(grid), dim3(128), 0, st, in_u8, m->w_conv1, m->b_conv1, U, B, sp[0], sp[1]);
             prof_close(m, st);
             LAUNCH_CHECK();
             RUN(tap("block1_conv1_act", U, sp[1], 32, 1));
@@ -498,8 +499,8 @@ template <typename T> struct Runner {
             size_t smem = (2048 + 8 * 128 + 128) * sizeof(float);
             prof_open(m, st, PC_HEAD, 2.0 * B * (2048.0 * (m->cfg.head_inner > 0 ? m->cfg.head_inner : 10)),
                       (double)B * H * H * 2048 * sizeof(T));
-            k_gap_head<T><<<B, 256, smem, st>>>(U, H * H, 2048, m->W1, m->b1, m->cfg.head_inner, m->W2, m->b2, 10,
-                                                feat, d_logits);
+            launch_k(k_gap_head<T>, dim3(B), dim3(256), smem, st, U, H * H, 2048, m->W1, m->b1, m->cfg.head_inner, m->W2, m->b2, 10, feat,
+                     d_logits);
             prof_close(m, st);
             LAUNCH_CHECK();
         }
@@ -735,6 +736,7 @@ extern "C" int kdl_create(const KdlConfig *cfg, KdlModel **out) {
     CK(cudaFuncSetAttribute(k_gap_head<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
     CK(cudaFuncSetAttribute(k_gap_head<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
     { const char *e1 = getenv("KDL_GEMM_VARIANT"); m->gemm_variant = e1 ? atoi(e1) : 1; }
+    { const char *e1 = getenv("KDL_PDL"); m->use_pdl = e1 && e1[0] == '1'; }
     { const char *e1 = getenv("KDL_CONV2_TAPS"); m->conv_shifted_taps = e1 && e1[0] == '1'; }
     { const char *e1 = getenv("KDL_MICROBATCH_MB"); m->microbatch_mb = e1 ? atoi(e1) : 0; }
     { const char *e1 = getenv("KDL_NO_FUSED_SEPCONV"); m->no_fused_sepconv = e1 && e1[0] == '1'; }
@@ -834,6 +836,10 @@ extern "C" int kdl_preprocess_u8(KdlModel *m, const uint8_t *d_src, const int64_
 }
 
 static int run_forward_eager(KdlModel *m, const float *in_f32, const uint8_t *in_u8, int B, float *d_logits, cudaStream_t st) {
+    struct PdlScope {  // programmatic dependent launch for the kernels of this forward pass (tensor-core path only)
+        PdlScope(bool on) { pdl_enabled() = on; }
+        ~PdlScope() { pdl_enabled() = false; }
+    } pdl_scope(m->use_pdl && m->cfg.precision == KDL_PRECISION_BF16 && m->cfg.gemm_impl == KDL_GEMM_AUTO && !m->profiling);
     if (m->cfg.precision == KDL_PRECISION_F32) {
         Runner<float> r{m, st, B};
         return r.forward(in_f32, in_u8, d_logits);

@@ -314,6 +314,8 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     tc_fence_after();
     uint32_t tmem_base;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+    pdl_launch_dependents();
+    pdl_wait();  // everything above overlapped the previous kernel; global memory is touched only from here on
 
     if (warp == 0) {
         // ================= TMA producer =================
@@ -540,11 +542,11 @@ inline int launch_gemm(const TmaEncoder &enc, const bf16 *A, const CUtensorMap *
     const int tiles = ((M + BLOCK_M - 1) / BLOCK_M) * ((N + BLOCK_N - 1) / BLOCK_N);
     const int grid = tiles < num_sms() ? tiles : num_sms();
     if (K <= 256)  // HBM-bound: more stores in flight matter more than ring depth
-        k_gemm_tc<128, 256, false, 3, 4><<<grid, NUM_THREADS, CfgHbm::SMEM_BYTES, st>>>(tmA, *tmB, tmOut, bias, residual, out, M, N, K,
-                                                                                        relu, ConvGeom{0, 0, 0, 0}, ldo);
+        launch_k(k_gemm_tc<128, 256, false, 3, 4>, dim3(grid), dim3(NUM_THREADS), CfgHbm::SMEM_BYTES, st, tmA, *tmB, tmOut, bias, residual, out,
+                 M, N, K, relu, ConvGeom{0, 0, 0, 0}, ldo);
     else
-        k_gemm_tc<128, 256, false><<<grid, NUM_THREADS, CfgStd::SMEM_BYTES, st>>>(tmA, *tmB, tmOut, bias, residual, out, M, N, K, relu,
-                                                                                  ConvGeom{0, 0, 0, 0}, ldo);
+        launch_k(k_gemm_tc<128, 256, false>, dim3(grid), dim3(NUM_THREADS), CfgStd::SMEM_BYTES, st, tmA, *tmB, tmOut, bias, residual, out, M, N,
+                 K, relu, ConvGeom{0, 0, 0, 0}, ldo);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         snprintf(err, 512, "k_gemm_tc launch (M=%d N=%d K=%d): %s", M, N, K, cudaGetErrorString(e));

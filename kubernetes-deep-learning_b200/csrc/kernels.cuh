@@ -114,6 +114,8 @@ k_conv1(const TIn *__restrict__ in, const float *__restrict__ w /*[27][32]*/, co
     if (threadIdx.x < 32) bs[threadIdx.x] = bias[threadIdx.x];
     for (int i = threadIdx.x; i < 256; i += blockDim.x) lut[i] = scale_px((uint8_t)i);
     __syncthreads();
+    pdl_launch_dependents();
+    pdl_wait();
     const long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const long long npix = (long long)B * Ho * Ho;
     if (pix >= npix) return;
@@ -250,6 +252,8 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 k_subsample2(const T *__restrict__ in, T *__restrict__ out, int B, int H, int W, int C, int ld, int Ho, int Wo) {
     const int CV = C >> 2;
+    pdl_launch_dependents();
+    pdl_wait();
     long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     long long total = (long long)B * Ho * Wo * CV;
     if (t >= total) return;
@@ -376,6 +380,8 @@ k_gap_head(const T *__restrict__ in, int HW, int C, const float *__restrict__ W1
     float *part = sm + C;        // [8][128]
     float *hid = part + 8 * 128; // [128]
     const int b = blockIdx.x, tid = threadIdx.x;
+    pdl_launch_dependents();
+    pdl_wait();
     const T *base = in + (size_t)b * HW * C;
     const float inv = 1.0f / (float)HW;
     for (int c = tid * 4; c < C; c += blockDim.x * 4) {

@@ -86,6 +86,8 @@ k_pool_tma(const __grid_constant__ CUtensorMap tmIn, const __grid_constant__ CUt
         tc::fence_barrier_init();
     }
     __syncthreads();
+    pdl_launch_dependents();
+    pdl_wait();
     if (warp == n_cwarps) {
         if (lane == 0) {
             int stage = 0;
@@ -210,7 +212,7 @@ inline int launch(const tc::TmaEncoder &enc, const bf16 *in, const bf16 *res, bf
     if (per_sm < 1) per_sm = 1;
     const int cap = tc::num_sms() * per_sm;
     const int grid = p.total_tiles < cap ? p.total_tiles : cap;
-    k_pool_tma<<<grid, p.consumer_threads + 32, smem_bytes(p), st>>>(tm, tmr, out, sub, p);
+    launch_k(k_pool_tma, dim3(grid), dim3(p.consumer_threads + 32), smem_bytes(p), st, tm, tmr, out, sub, p);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         snprintf(err, 512, "k_pool_tma launch (B=%d H=%d C=%d threads=%d smem=%u): %s", B, H, C, p.consumer_threads + 32, smem_bytes(p),

@@ -96,6 +96,8 @@ k_sepconv_tc(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
     tc_fence_after();
     uint32_t tmem_base;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+    pdl_launch_dependents();
+    pdl_wait();
 
     if (warp == 0) {
         // ================= TMA producer =================
@@ -318,8 +320,8 @@ inline int launch(const TmaEncoder &enc, const bf16 *in, const float *dwpad, con
         }
     }
     const int grid = g.num_tiles < num_sms() ? g.num_tiles : num_sms();
-    if (relu_in) k_sepconv_tc<true><<<grid, NUM_THREADS_SEP, SMEM_BYTES, st>>>(tmX, *tmB, tmOut, dwpad, bias, g);
-    else k_sepconv_tc<false><<<grid, NUM_THREADS_SEP, SMEM_BYTES, st>>>(tmX, *tmB, tmOut, dwpad, bias, g);
+    if (relu_in) launch_k(k_sepconv_tc<true>, dim3(grid), dim3(NUM_THREADS_SEP), SMEM_BYTES, st, tmX, *tmB, tmOut, dwpad, bias, g);
+    else launch_k(k_sepconv_tc<false>, dim3(grid), dim3(NUM_THREADS_SEP), SMEM_BYTES, st, tmX, *tmB, tmOut, dwpad, bias, g);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         snprintf(err, 512, "k_sepconv_tc launch (B=%d H=%d K=%d N=%d): %s", B, H, K, N, cudaGetErrorString(e));

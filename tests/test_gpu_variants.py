@@ -37,7 +37,7 @@ def test_kernel_variants_are_bit_identical():
     u8, _ = synth_inputs(299, 5)
     base = _logits({}, W, u8)
     for env in ({"KDL_NO_FUSED_SEPCONV": "1"}, {"KDL_GEMM_VARIANT": "2"}, {"KDL_GEMM_VARIANT": "3"}, {"KDL_CONV2_TAPS": "1"},
-                {"KDL_MICROBATCH_MB": "8"}):
+                {"KDL_MICROBATCH_MB": "8"}, {"KDL_PDL": "1"}):
         got = _logits(env, W, u8)
         np.testing.assert_array_equal(got, base, err_msg=str(env))
 
