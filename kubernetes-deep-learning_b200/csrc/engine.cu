@@ -687,6 +687,17 @@ extern "C" int kdl_create(const KdlConfig *cfg, KdlModel **out) {
     }
     KdlModel *m = new (std::nothrow) KdlModel();
     if (!m) { set_err(g_err, "kdl_create: out of host memory"); return KDL_ENOMEM; }
+    for (int i = 0; i < KdlModel::NSLOT; ++i) m->slot_ev[i] = nullptr;
+    // from here on a failure must release what was built: CKM = CK + kdl_destroy
+#define CKM(call)                                                                                        \
+    do {                                                                                                 \
+        cudaError_t e_ = (call);                                                                         \
+        if (e_ != cudaSuccess) {                                                                         \
+            set_err(g_err, "%s:%d %s -> %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_));         \
+            kdl_destroy(m);                                                                              \
+            return KDL_ECUDA;                                                                            \
+        }                                                                                                \
+    } while (0)
     m->cfg = *cfg;
     m->err[0] = 0;
     err = m->err;
@@ -729,18 +740,19 @@ extern "C" int kdl_create(const KdlConfig *cfg, KdlModel **out) {
         return rc;
     }
     for (int i = 0; i < KdlModel::NSLOT; ++i) {
-        CK(cudaMallocHost((void **)&m->h_meta[i], MB * sizeof(ImgMeta)));
-        CK(cudaEventCreateWithFlags(&m->slot_ev[i], cudaEventDisableTiming));
+        CKM(cudaMallocHost((void **)&m->h_meta[i], MB * sizeof(ImgMeta)));
+        CKM(cudaEventCreateWithFlags(&m->slot_ev[i], cudaEventDisableTiming));
     }
-    CK(cudaStreamCreateWithFlags(&m->own_stream, cudaStreamNonBlocking));
-    CK(cudaFuncSetAttribute(k_gap_head<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
-    CK(cudaFuncSetAttribute(k_gap_head<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
+    CKM(cudaStreamCreateWithFlags(&m->own_stream, cudaStreamNonBlocking));
+    CKM(cudaFuncSetAttribute(k_gap_head<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
+    CKM(cudaFuncSetAttribute(k_gap_head<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
     { const char *e1 = getenv("KDL_GEMM_VARIANT"); m->gemm_variant = e1 ? atoi(e1) : 1; }
     { const char *e1 = getenv("KDL_PDL"); m->use_pdl = e1 && e1[0] == '1'; }
     { const char *e1 = getenv("KDL_CONV2_TAPS"); m->conv_shifted_taps = e1 && e1[0] == '1'; }
     { const char *e1 = getenv("KDL_MICROBATCH_MB"); m->microbatch_mb = e1 ? atoi(e1) : 0; }
     { const char *e1 = getenv("KDL_NO_FUSED_SEPCONV"); m->no_fused_sepconv = e1 && e1[0] == '1'; }
     if ((rc = tc::configure(m->err)) != KDL_OK || (rc = tc2::configure2(m->err)) != KDL_OK || (rc = tcm2::configure(m->err)) != KDL_OK || (rc = convtc::configure(m->err)) != KDL_OK || (rc = dwt::configure(m->err)) != KDL_OK || (rc = poolt::configure(m->err)) != KDL_OK || (rc = sepc::configure(m->err)) != KDL_OK) { set_err(g_err, "%s", m->err); kdl_destroy(m); return rc; }
+#undef CKM
     *out = m;
     return KDL_OK;
 }
@@ -753,7 +765,8 @@ extern "C" int kdl_destroy(KdlModel *m) {
     if (m->d_src) cudaFree(m->d_src);
     if (m->d_in_f32) cudaFree(m->d_in_f32);
     for (int i = 0; i < KdlModel::NSLOT; ++i) {
-        if (m->h_meta[i]) { cudaFreeHost(m->h_meta[i]); cudaEventDestroy(m->slot_ev[i]); }
+        if (m->h_meta[i]) cudaFreeHost(m->h_meta[i]);
+        if (m->slot_ev[i]) cudaEventDestroy(m->slot_ev[i]);
     }
     if (m->own_stream) cudaStreamDestroy(m->own_stream);
     for (cudaEvent_t e : m->ev_pool) cudaEventDestroy(e);

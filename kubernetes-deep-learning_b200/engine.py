@@ -30,7 +30,9 @@ class PackedImages:
     """B decoded RGB uint8 images of arbitrary sizes packed into one (pinned) host buffer, plus the
     per-image metadata arrays the C ABI takes.  Offsets are 256-byte aligned."""
 
-    def __init__(self, images: Sequence[np.ndarray], pinned: bool = True):
+    def __init__(self, images: Sequence[np.ndarray], pinned: bool = True, staging: Optional[torch.Tensor] = None):
+        """`staging`: an existing (pinned) uint8 CPU tensor to pack into instead of allocating one -- pinning memory costs far more
+        than a batch-1 forward pass, so request paths reuse one buffer (Model.pack)."""
         self.B = len(images)
         self.h = np.empty(self.B, np.int32)
         self.w = np.empty(self.B, np.int32)
@@ -45,7 +47,10 @@ class PackedImages:
             self.offset[i] = off
             off += (im.shape[0] * im.shape[1] * 3 + 255) // 256 * 256
         self.total_bytes = max(off, 256)
-        self.host = torch.empty(self.total_bytes, dtype=torch.uint8, pin_memory=pinned and torch.cuda.is_available())
+        if staging is not None and staging.numel() >= self.total_bytes:
+            self.host = staging
+        else:
+            self.host = torch.empty(self.total_bytes, dtype=torch.uint8, pin_memory=pinned and torch.cuda.is_available())
         hv = self.host.numpy()
         for i, im in enumerate(images):
             n = im.shape[0] * im.shape[1] * 3
@@ -175,10 +180,19 @@ class Model:
         """Retires the oldest in-flight `submit_packed_host`."""
         _lib.check(self.lib.kdl_wait(self.h), self.h)
 
+    def pack(self, images: Sequence[np.ndarray]) -> PackedImages:
+        """Packs into this model's reusable pinned staging buffer (grown on demand).  The returned object is valid until the next
+        `pack` call -- exactly what the synchronous request path needs."""
+        need = sum((im.shape[0] * im.shape[1] * 3 + 255) // 256 * 256 for im in images) or 256
+        st = getattr(self, "_staging", None)
+        if st is None or st.numel() < need:
+            self._staging = torch.empty(int(need * 1.25) + 256, dtype=torch.uint8, pin_memory=True)
+        return PackedImages(images, staging=self._staging)
+
     def predict_uint8(self, images: Sequence[np.ndarray]) -> np.ndarray:
         outs = []
         for i in range(0, len(images), self.max_batch):
-            outs.append(self.predict_packed_host(PackedImages(images[i:i + self.max_batch])))
+            outs.append(self.predict_packed_host(self.pack(images[i:i + self.max_batch])))
         return np.concatenate(outs, 0) if outs else np.empty((0, 10), np.float32)
 
     def profile_begin(self):
