@@ -33,8 +33,12 @@ constexpr uint32_t BIAS_BYTES = BN * 4;
 constexpr uint32_t SMEM_BYTES = NA * A_BYTES + NB * B_BYTES + EPI_BYTES + NX * XSTAGE + BIAS_BYTES + 256 + 1024;
 static_assert(SMEM_BYTES <= 232448, "exceeds 227 KB");
 static_assert(XSTAGE % 128 == 0, "TMA destinations must stay 128-byte aligned");
-constexpr int NUM_THREADS_SEP = 14 * 32;
-constexpr int DW_WARPS = 8;
+#ifndef KDL_SEP_DW_WARPS
+#define KDL_SEP_DW_WARPS 8
+#endif
+constexpr int DW_WARPS = KDL_SEP_DW_WARPS;             // 8 = two 4-row strips, 12 = three strips (3,3,2 rows): more warps to hide LDS/FMA latency
+constexpr int DW_ROWS = DW_WARPS == 8 ? 4 : 3;
+constexpr int NUM_THREADS_SEP = (6 + DW_WARPS) * 32;
 
 struct Geom {
     int B, H, W, K, N;       // spatial size (stride 1, SAME), channels in / out
@@ -198,11 +202,11 @@ k_sepconv_tc(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
         if (lane == 0) bulk_wait_all<0>();
     } else {
         // ================= depthwise producers (warps 6..13) =================
-        const int dt = threadIdx.x - 6 * 32;      // 0..255
+        const int dt = threadIdx.x - 6 * 32;      // 0..32*DW_WARPS-1
         const int cg = dt & 15;                   // 4-channel group of the 64-channel chunk
         const int cp = (dt >> 4) & 7;             // column pair
-        const int y_lo = (dt >> 7) * 4;           // strip of 4 output rows
-        const int y_hi = y_lo + 4;
+        const int y_lo = (dt >> 7) * DW_ROWS;     // strip of output rows
+        const int y_hi = min(y_lo + DW_ROWS, TH);
         int xs = 0, as = 0;
         uint32_t xph = 0, aph = 0;
         for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x) {
