@@ -25,7 +25,8 @@ static_assert(SMEM_BYTES <= 232448, "exceeds 227 KB");
 
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 k_conv3x3_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const float *__restrict__ bias,
-             bf16 *__restrict__ out, int M, int relu, ConvGeom cg, int box_rows) {
+             bf16 *__restrict__ out, bf16 *__restrict__ sub /*nullable: compact copy of the even pixels*/, int M, int relu, ConvGeom cg,
+             int box_rows) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t stage_bytes = 2u * (uint32_t)box_rows * ROWB;  // multiple of 128
@@ -129,9 +130,16 @@ k_conv3x3_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             if (lane == 0) mbar_arrive(tempty_bar(acc));  // accumulator is in registers: release it before the stores
             if (row < M && y < cg.Hout && x < cg.Wout) {
                 bf16 *o = out + ((size_t)(b * cg.Hout + y) * cg.Wout + x) * COUT;
+                // the next block's Conv2D(1x1, strides 2) reads only the even pixels: emit them compactly here instead of a separate pass
+                bf16 *os = (sub && !(y & 1) && !(x & 1))
+                               ? sub + ((size_t)(b * ((cg.Hout + 1) >> 1) + (y >> 1)) * ((cg.Wout + 1) >> 1) + (x >> 1)) * COUT
+                               : nullptr;
 #pragma unroll
-                for (int g = 0; g < 8; ++g)
-                    *reinterpret_cast<uint4 *>(o + g * 8) = epi8(r + g * 8, bias_base + 32u * g, relu, false, make_uint4(0, 0, 0, 0));
+                for (int g = 0; g < 8; ++g) {
+                    const uint4 v = epi8(r + g * 8, bias_base + 32u * g, relu, false, make_uint4(0, 0, 0, 0));
+                    *reinterpret_cast<uint4 *>(o + g * 8) = v;
+                    if (os) *reinterpret_cast<uint4 *>(os + g * 8) = v;
+                }
             }
         }
     }
@@ -155,8 +163,8 @@ inline int configure(char *err) {
 inline bool geometry_supported(int Win) { return 128 + 2 * Win + 2 <= 512; }
 
 // in [B,Hin,Win,32] bf16; weights via tmB (box 32 x 64 over Wt[64][288(+pad)], 64B swizzle); out [B,Hin-2,Win-2,64]
-inline int launch(const TmaEncoder &enc, const bf16 *in, const CUtensorMap *tmB, const float *bias, bf16 *out, int B, int Hin, int Win,
-                  int relu, cudaStream_t st, char *err) {
+inline int launch(const TmaEncoder &enc, const bf16 *in, const CUtensorMap *tmB, const float *bias, bf16 *out, bf16 *sub, int B, int Hin,
+                  int Win, int relu, cudaStream_t st, char *err) {
     const int M = B * Hin * Win;
     const int halo_rows = BLOCK_M + 2 * Win + 2;
     const int box_rows = ((halo_rows + 1) / 2 + 7) & ~7;  // multiple of 8 rows: both boxes start on a 512-byte swizzle-pattern boundary
@@ -167,8 +175,8 @@ inline int launch(const TmaEncoder &enc, const bf16 *in, const CUtensorMap *tmB,
     }
     const int tiles = (M + BLOCK_M - 1) / BLOCK_M;
     const int grid = tiles < num_sms() ? tiles : num_sms();
-    launch_k(k_conv3x3_tc, dim3(grid), dim3(NUM_THREADS), SMEM_BYTES, st, tmA, *tmB, bias, out, M, relu, ConvGeom{Hin, Win, Hin - 2, Win - 2},
-             box_rows);
+    launch_k(k_conv3x3_tc, dim3(grid), dim3(NUM_THREADS), SMEM_BYTES, st, tmA, *tmB, bias, out, sub, M, relu,
+             ConvGeom{Hin, Win, Hin - 2, Win - 2}, box_rows);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         snprintf(err, 512, "k_conv3x3_tc launch (B=%d H=%d): %s", B, Hin, cudaGetErrorString(e));

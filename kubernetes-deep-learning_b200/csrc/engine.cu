@@ -393,7 +393,7 @@ template <typename T> struct Runner {
         char name[64];
         // ---- block1 ----
         {
-            long long threads = (long long)B * sp[1] * sp[1];
+            long long threads = (long long)B * sp[1] * ((sp[1] + 1) / 2);  // one thread per pair of output pixels
             unsigned grid = (unsigned)((threads + 127) / 128);
             prof_open(m, st, PC_CONV1, 2.0 * 27 * 32 * B * sp[1] * sp[1],
                       (double)B * sp[0] * sp[0] * 3 * (in_f32 ? 4 : 1) + (double)B * sp[1] * sp[1] * 32 * sizeof(T));
@@ -407,7 +407,7 @@ template <typename T> struct Runner {
                 prof_open(m, st, PC_CONV2, 2.0 * B * sp[2] * sp[2] * 288.0 * 64.0,
                           ((double)B * sp[1] * sp[1] * 32 + (double)B * sp[2] * sp[2] * 64 + 288.0 * 64) * 2.0);
                 int rc = (convtc::geometry_supported(sp[1]) && !m->conv_shifted_taps)
-                             ? convtc::launch(m->tma, (const bf16 *)U, &m->conv2.tmB, m->conv2.bias, (bf16 *)X, B, sp[1], sp[1], 1, st, m->err)
+                             ? convtc::launch(m->tma, (const bf16 *)U, &m->conv2.tmB, m->conv2.bias, (bf16 *)X, (bf16 *)m->S, B, sp[1], sp[1], 1, st, m->err)
                              : tc::launch_conv3x3(m->tma, (const bf16 *)U, &m->conv2.tmB, m->conv2.bias, (bf16 *)X, B, sp[1], sp[1], 1, st, m->err);
                 prof_close(m, st);
                 if (rc != KDL_OK) return rc;
@@ -419,7 +419,8 @@ template <typename T> struct Runner {
         }
         // ---- entry/exit blocks with projection + pool: 2,3,4 then middle, then 13 ----
         int si = 0;  // sepconv index
-        bool have_sub = false;  // S already holds the even pixels of X (written by the previous block's pool kernel)
+        // S already holds the even pixels of X when the producer of X wrote them (conv2's epilogue, the pool kernels of blocks 2-3)
+        bool have_sub = use_tc() && convtc::geometry_supported(sp[1]) && !m->conv_shifted_taps;
         auto entry_block = [&](int blk, int ri, int H, int Ho) -> int {
             const GemmW &rg = m->res[ri];
             RUN(projection(X, rg, R, H, Ho, have_sub));

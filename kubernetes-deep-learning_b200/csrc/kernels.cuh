@@ -101,8 +101,8 @@ template <> struct InPx<uint8_t> {  // the gateway's x/127.5-1 through a 256-ent
     static __device__ __forceinline__ float get(const uint8_t *p, const float *lut) { return lut[__ldg(p)]; }
 };
 
-// One thread = one output pixel x all 32 output channels (27 inputs x 32 FMAs, weights broadcast from shared memory);
-// a warp writes 32 adjacent pixels = 2 KB contiguous.
+// One thread = two horizontally adjacent output pixels x all 32 output channels: every weight vector read from shared memory feeds
+// two pixels (the kernel is bound by shared-memory weight reads + fp32 FMA issue, not by HBM), and the two 3x3 windows share a column.
 template <typename TIn, typename T>
 __global__ void __launch_bounds__(128)
 k_conv1(const TIn *__restrict__ in, const float *__restrict__ w /*[27][32]*/, const float *__restrict__ bias,
@@ -116,38 +116,52 @@ k_conv1(const TIn *__restrict__ in, const float *__restrict__ w /*[27][32]*/, co
     __syncthreads();
     pdl_launch_dependents();
     pdl_wait();
-    const long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    const long long npix = (long long)B * Ho * Ho;
-    if (pix >= npix) return;
-    const int b = (int)(pix / (Ho * Ho));
-    const int r = (int)(pix - (long long)b * Ho * Ho);
-    const int oy = r / Ho, ox = r - oy * Ho;
+    const int Wp = (Ho + 1) >> 1;  // pixel pairs per output row
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long npairs = (long long)B * Ho * Wp;
+    if (t >= npairs) return;
+    const int b = (int)(t / ((long long)Ho * Wp));
+    const int r = (int)(t - (long long)b * Ho * Wp);
+    const int oy = r / Wp, ox = (r - oy * Wp) * 2;
+    const bool two = ox + 1 < Ho;
     const TIn *base = in + (((long long)b * S + 2 * oy) * S + 2 * ox) * 3;
-    float v[27];
+    // 3 rows x 5 input pixels x 3 channels; the second window starts 2 pixels (6 values) to the right
+    float v[3][15];
 #pragma unroll
     for (int ky = 0; ky < 3; ++ky)
 #pragma unroll
-        for (int kk = 0; kk < 9; ++kk) v[ky * 9 + kk] = InPx<TIn>::get(base + (long long)ky * S * 3 + kk, lut);
-    // packed fp32 FMAs (fma.rn.f32x2): 16 per input value instead of 32 scalar ones -- this kernel is FMA-issue bound
-    float2 acc[16];
+        for (int kk = 0; kk < 15; ++kk) v[ky][kk] = (kk < 9 || two) ? InPx<TIn>::get(base + (long long)ky * S * 3 + kk, lut) : 0.f;
+    float2 acc0[16], acc1[16];
 #pragma unroll
-    for (int c = 0; c < 16; ++c) acc[c] = *reinterpret_cast<const float2 *>(&bs[c * 2]);
+    for (int c = 0; c < 16; ++c) acc0[c] = acc1[c] = *reinterpret_cast<const float2 *>(&bs[c * 2]);
 #pragma unroll
-    for (int k = 0; k < 27; ++k) {
-        const float4 *wp = reinterpret_cast<const float4 *>(&ws[k * 32]);
-        const float2 a = make_float2(v[k], v[k]);
+    for (int ky = 0; ky < 3; ++ky) {
 #pragma unroll
-        for (int c = 0; c < 8; ++c) {
-            const float4 w4 = wp[c];
-            acc[2 * c] = ffma2(a, make_float2(w4.x, w4.y), acc[2 * c]);
-            acc[2 * c + 1] = ffma2(a, make_float2(w4.z, w4.w), acc[2 * c + 1]);
+        for (int kk = 0; kk < 9; ++kk) {
+            const float4 *wp = reinterpret_cast<const float4 *>(&ws[(ky * 9 + kk) * 32]);
+            const float2 a0 = make_float2(v[ky][kk], v[ky][kk]), a1 = make_float2(v[ky][kk + 6], v[ky][kk + 6]);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const float4 w4 = wp[c];
+                const float2 wlo = make_float2(w4.x, w4.y), whi = make_float2(w4.z, w4.w);
+                acc0[2 * c] = ffma2(a0, wlo, acc0[2 * c]);
+                acc0[2 * c + 1] = ffma2(a0, whi, acc0[2 * c + 1]);
+                acc1[2 * c] = ffma2(a1, wlo, acc1[2 * c]);
+                acc1[2 * c + 1] = ffma2(a1, whi, acc1[2 * c + 1]);
+            }
         }
     }
-    T *o = out + pix * 32;
+    T *o = out + (((long long)b * Ho + oy) * Ho + ox) * 32;
 #pragma unroll
     for (int c = 0; c < 4; ++c)
-        st8<T>(o + c * 8, relu4(make_float4(acc[4 * c].x, acc[4 * c].y, acc[4 * c + 1].x, acc[4 * c + 1].y)),
-               relu4(make_float4(acc[4 * c + 2].x, acc[4 * c + 2].y, acc[4 * c + 3].x, acc[4 * c + 3].y)));
+        st8<T>(o + c * 8, relu4(make_float4(acc0[4 * c].x, acc0[4 * c].y, acc0[4 * c + 1].x, acc0[4 * c + 1].y)),
+               relu4(make_float4(acc0[4 * c + 2].x, acc0[4 * c + 2].y, acc0[4 * c + 3].x, acc0[4 * c + 3].y)));
+    if (two) {
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+            st8<T>(o + 32 + c * 8, relu4(make_float4(acc1[4 * c].x, acc1[4 * c].y, acc1[4 * c + 1].x, acc1[4 * c + 1].y)),
+                   relu4(make_float4(acc1[4 * c + 2].x, acc1[4 * c + 2].y, acc1[4 * c + 3].x, acc1[4 * c + 3].y)));
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------
