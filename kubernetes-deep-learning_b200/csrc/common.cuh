@@ -102,6 +102,9 @@ inline cudaError_t launch_k(void (*kernel)(Params...), dim3 grid, dim3 block, si
 
 // packed fp32 FMA (Blackwell FFMA2): d = a * b + c on two lanes
 __device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+#ifdef KDL_SCALAR_FMA
+    return make_float2(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y));
+#endif
     unsigned long long d;
     asm("fma.rn.f32x2 %0, %1, %2, %3;"
         : "=l"(d)
