@@ -58,7 +58,7 @@ def test_cuda_graph_replay_equals_eager():
         m.close()
 
 
-@pytest.mark.parametrize("size", [96, 224, 331])
+@pytest.mark.parametrize("size", [96, 224, 331, 512])   # 512: conv2 falls back to the shifted-taps kernel (halo > 512 rows)
 def test_other_input_sizes_against_oracle(size):
     """Sizes other than 299/150 walk every tile-edge / padding path of the TMA kernels (224: 111,109,55,28,14,7; 96: 47,45,23,12,6,3).
     The fp32 path pins the geometry against the oracle at 1e-4.  Against the fp64 oracle the bf16 logit error grows as the final
@@ -67,14 +67,15 @@ def test_other_input_sizes_against_oracle(size):
     from kdl_b200 import engine, weights
     from oracle import xception_oracle as xo
     W = weights.make_weights(1, "calibrated")
-    u8, x = synth_inputs(size, 4)
+    n_img = 4 if size < 400 else 2
+    u8, x = synth_inputs(size, n_img)
     want = xo.forward(W, x, torch.float64)
     m = engine.Model(W, max_batch=4, input_size=size, precision="f32")
     try:
         gf = m.serving_default(input_8=x)["dense_7"]
     finally:
         m.close()
-    for i in range(4):
+    for i in range(n_img):
         assert rel(gf[i], want[i]) <= 1e-4
     # bf16 tensor-core path, layer by layer: few rounding steps have accumulated in the entry flow, so a tile-edge or padding bug
     # would stand out against the ~5e-3 rounding noise; deeper taps and the logits get the looser sanity bound
@@ -91,7 +92,7 @@ def test_other_input_sizes_against_oracle(size):
             assert e <= (1.2e-2 if early else 5e-2), (name, e)
     finally:
         mt.close()
-    for i in range(4):
+    for i in range(n_img):
         assert rel(got[i], want[i]) <= 5e-2
 
 
