@@ -5,7 +5,7 @@ import os
 from ctypes import POINTER, c_char_p, c_float, c_int32, c_int64, c_size_t, c_void_p
 
 _CSRC = os.path.join(os.path.dirname(os.path.abspath(__file__)), "csrc")
-LIB_PATH = os.path.join(_CSRC, "libkdl.so")
+LIB_PATH = os.environ.get("KDL_LIB", os.path.join(_CSRC, "libkdl.so"))   # KDL_LIB: alternative build (kernel experiments)
 
 KDL_OK, KDL_EINVAL, KDL_ECUDA, KDL_ESTATE, KDL_ENOMEM = 0, -1, -2, -3, -4
 PRECISION_F32, PRECISION_BF16 = 0, 1
