@@ -86,6 +86,7 @@ struct GemmW {
     float *bias = nullptr; // folded BN shift
     CUtensorMap tmB;       // TMA descriptor of Wnk (box 64 x 256: single-CTA kernel)
     CUtensorMap tmB2;      // TMA descriptor of Wnk (box 64 x 128: each CTA of a pair loads half of the N tile)
+    CUtensorMap tmB64;     // TMA descriptor of Wnk (box 64 x 64: small-M tiling)
 };
 
 struct Tap {
@@ -126,6 +127,7 @@ struct KdlModel {
     size_t d_src_cap = 0;
     float *d_in_f32 = nullptr;    // staging for kdl_forward_host
     float *d_logits = nullptr;
+    float *head_partial = nullptr;  // [max_batch][16][HEAD_MAXN] partial sums of the first dense layer
     ImgMeta *d_meta = nullptr;
     int32_t *d_xtab = nullptr, *d_ytab = nullptr;
     static const int NSLOT = 4;
@@ -162,7 +164,7 @@ struct KdlModel {
 
 enum ProfClass { PC_RESIZE = 0, PC_CONV1, PC_CONV2, PC_DW, PC_PW_TC_HBM, PC_PW_TC_TENSOR, PC_GEMM_SIMPLE, PC_SUBSAMPLE, PC_POOL, PC_HEAD, PC_SEPFUSED, PC_COUNT };
 static const char *PROF_NAMES[PC_COUNT] = {"k_resize", "k_conv1", "conv2_implicit_gemm", "k_dw3x3", "k_gemm_tc[K<=256,hbm-bound]",
-                                           "k_gemm_tc[K>=728,tensor-bound]", "k_gemm_simple", "k_subsample2", "k_maxpool_add", "k_gap_head",
+                                           "k_gemm_tc[K>=728,tensor-bound]", "k_gemm_simple", "k_subsample2", "k_maxpool_add", "k_gap_partial+k_head_finish",
                                            "k_sepconv_tc[fused dw+pw,hbm-bound]"};
 
 static cudaEvent_t prof_event(KdlModel *m) {
@@ -295,7 +297,7 @@ template <typename T> struct Runner {
                                        st, m->err, ld(g.K), ld(g.N));
             else
                 rc = tc::launch_gemm(m->tma, (const bf16 *)A, &g.tmB, g.bias, (const bf16 *)resid, (bf16 *)out,
-                                     M, g.N, g.K, relu, st, m->err, ld(g.K), ld(g.N));
+                                     M, g.N, g.K, relu, st, m->err, ld(g.K), ld(g.N), &g.tmB64);
             prof_close(m, st);
             if (rc != KDL_OK) return rc;
             m->launches++;
@@ -497,11 +499,12 @@ template <typename T> struct Runner {
                 RUN(alloc_tap("avg_pool", 1, 2048, 0, true, &i));
                 feat = (float *)m->taps[i].buf;
             }
-            size_t smem = (2048 + 8 * 128 + 128) * sizeof(float);
-            prof_open(m, st, PC_HEAD, 2.0 * B * (2048.0 * (m->cfg.head_inner > 0 ? m->cfg.head_inner : 10)),
-                      (double)B * H * H * 2048 * sizeof(T));
-            launch_k(k_gap_head<T>, dim3(B), dim3(256), smem, st, U, H * H, 2048, m->W1, m->b1, m->cfg.head_inner, m->W2, m->b2, 10, feat,
-                     d_logits);
+            const int hi = m->cfg.head_inner;
+            prof_open(m, st, PC_HEAD, 2.0 * B * (2048.0 * (hi > 0 ? hi : 10)), (double)B * H * H * 2048 * sizeof(T));
+            launch_k(k_gap_partial<T>, dim3(2048 / HEAD_SLICE, B), dim3(256), 0, st, U, H * H, 2048, hi > 0 ? m->W1 : m->W2, hi > 0 ? hi : 10, feat,
+                     m->head_partial);
+            m->launches++;
+            launch_k(k_head_finish, dim3(B), dim3(128), 0, st, m->head_partial, 2048 / HEAD_SLICE, m->b1, hi, m->W2, m->b2, 10, d_logits);
             prof_close(m, st);
             LAUNCH_CHECK();
         }
@@ -573,6 +576,7 @@ static int make_gemm(KdlModel *m, GemmW &g, const float *kern, int K, int N, con
         bool ok = conv3x3 ? m->tma.encode_2d(&g.tmB, g.Wnk, (uint64_t)K, (uint64_t)N, (uint64_t)Kp * 2, 32, 64, 64)
                           : m->tma.encode_2d(&g.tmB, g.Wnk, (uint64_t)K, (uint64_t)N, (uint64_t)Kp * 2, tc::BLOCK_K, tc::BLOCK_N, 128);
         if (ok && !conv3x3) ok = m->tma.encode_2d(&g.tmB2, g.Wnk, (uint64_t)K, (uint64_t)N, (uint64_t)Kp * 2, tc2::BK2, 128, 128);
+        if (ok && !conv3x3) ok = m->tma.encode_2d(&g.tmB64, g.Wnk, (uint64_t)K, (uint64_t)N, (uint64_t)Kp * 2, tc::BLOCK_K, 64, 128);
         if (!ok) {
             set_err(m->err, "cuTensorMapEncodeTiled failed for weight [%d,%d]", N, K);
             return KDL_ECUDA;
@@ -734,6 +738,7 @@ extern "C" int kdl_create(const KdlConfig *cfg, KdlModel **out) {
         (rc = dev_alloc(m, &m->S, (MB * sel + slack) * m->esz)) ||
         (rc = dev_alloc(m, (void **)&m->u8img, MB * sq(S) * 3 + 16)) ||
         (rc = dev_alloc(m, (void **)&m->d_logits, MB * 10 * 4)) ||
+        (rc = dev_alloc(m, (void **)&m->head_partial, MB * (2048 / HEAD_SLICE) * HEAD_MAXN * 4)) ||
         (rc = dev_alloc(m, (void **)&m->d_meta, MB * sizeof(ImgMeta) * KdlModel::NSLOT)) ||
         (rc = dev_alloc(m, (void **)&m->d_xtab, MB * S * 4)) || (rc = dev_alloc(m, (void **)&m->d_ytab, MB * S * 4))) {
         set_err(g_err, "%s", m->err);
@@ -745,8 +750,6 @@ extern "C" int kdl_create(const KdlConfig *cfg, KdlModel **out) {
         CKM(cudaEventCreateWithFlags(&m->slot_ev[i], cudaEventDisableTiming));
     }
     CKM(cudaStreamCreateWithFlags(&m->own_stream, cudaStreamNonBlocking));
-    CKM(cudaFuncSetAttribute(k_gap_head<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
-    CKM(cudaFuncSetAttribute(k_gap_head<bf16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384));
     { const char *e1 = getenv("KDL_GEMM_VARIANT"); m->gemm_variant = e1 ? atoi(e1) : 1; }
     { const char *e1 = getenv("KDL_PDL"); m->use_pdl = e1 && e1[0] == '1'; }
     { const char *e1 = getenv("KDL_CONV2_TAPS"); m->conv_shifted_taps = e1 && e1[0] == '1'; }
@@ -788,7 +791,7 @@ extern "C" int kdl_destroy(KdlModel *m) {
 extern "C" const char *kdl_last_error(const KdlModel *m) { return m ? m->err : g_err; }
 extern "C" int kdl_last_launch_count(const KdlModel *m) { return m ? m->launches : 0; }
 extern "C" const char *kdl_version(void) {
-    return "kdl 0.1 sm_100a: k_resize k_conv1 k_dw3x3 k_maxpool_add k_gap_head k_gemm_simple k_gemm_tc(tcgen05/TMEM/TMA)";
+    return "kdl 0.2 sm_100a: k_resize k_conv1 k_conv3x3_tc k_dw_tma k_sepconv_tc k_pool_tma k_gemm_tc(tcgen05/TMEM/TMA) k_gap_partial k_head_finish";
 }
 
 // ---------------------------------------------------------------------------------------------------

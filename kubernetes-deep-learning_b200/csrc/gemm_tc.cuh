@@ -55,6 +55,7 @@ template <int SW, int BN, bool CONV, int NST = (CONV ? 12 : 4), int EB = 2> stru
 };
 typedef Cfg<128, 256, false> CfgStd;
 typedef Cfg<128, 256, false, 3, 4> CfgHbm;
+typedef Cfg<128, 64, false, 4, 2> CfgSmallM;   // 128 x 64 tiles: 4x more CTAs and half the operand bytes per CTA when M is small (latency)
 typedef Cfg<64, 64, true> CfgConv;
 
 // geometry of the implicit-GEMM conv mode (ignored otherwise)
@@ -508,6 +509,8 @@ inline int configure(char *err) {
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(k_gemm_tc<128, 256, false, 3, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CfgHbm::SMEM_BYTES);
     if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(k_gemm_tc<128, 64, false, 4, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CfgSmallM::SMEM_BYTES);
+    if (e == cudaSuccess)
         e = cudaFuncSetAttribute(k_gemm_tc<64, 64, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CfgConv::SMEM_BYTES);
     if (e != cudaSuccess) {
         snprintf(err, 512, "cudaFuncSetAttribute(k_gemm_tc smem): %s", cudaGetErrorString(e));
@@ -529,8 +532,10 @@ inline int num_sms() {
 
 // standard GEMM: A [M,K] bf16 row-major, weights via tmB (box BLOCK_K x BLOCK_N over Wt[N,K]), out [M,N]
 // lda / ldo: row pitch (elements) of A and of out/residual; 0 = dense (K / N)
+// tmB64 (optional): the same weights with a 64-row box; used when the 128x256 tiling would leave most SMs idle (small M)
 inline int launch_gemm(const TmaEncoder &enc, const bf16 *A, const CUtensorMap *tmB, const float *bias, const bf16 *residual,
-                       bf16 *out, int M, int N, int K, int relu, cudaStream_t st, char *err, int lda = 0, int ldo = 0) {
+                       bf16 *out, int M, int N, int K, int relu, cudaStream_t st, char *err, int lda = 0, int ldo = 0,
+                       const CUtensorMap *tmB64 = nullptr) {
     if (lda == 0) lda = K;
     if (ldo == 0) ldo = N;
     CUtensorMap tmA, tmOut;
@@ -540,6 +545,18 @@ inline int launch_gemm(const TmaEncoder &enc, const bf16 *A, const CUtensorMap *
         return KDL_ECUDA;
     }
     const int tiles = ((M + BLOCK_M - 1) / BLOCK_M) * ((N + BLOCK_N - 1) / BLOCK_N);
+    if (tmB64 && tiles * 2 < num_sms()) {
+        const int tiles64 = ((M + BLOCK_M - 1) / BLOCK_M) * ((N + 63) / 64);
+        const int grid64 = tiles64 < num_sms() ? tiles64 : num_sms();
+        launch_k(k_gemm_tc<128, 64, false, 4, 2>, dim3(grid64), dim3(NUM_THREADS), CfgSmallM::SMEM_BYTES, st, tmA, *tmB64, tmOut, bias, residual,
+                 out, M, N, K, relu, ConvGeom{0, 0, 0, 0}, ldo);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) {
+            snprintf(err, 512, "k_gemm_tc<small-M> launch (M=%d N=%d K=%d): %s", M, N, K, cudaGetErrorString(e));
+            return KDL_ECUDA;
+        }
+        return KDL_OK;
+    }
     const int grid = tiles < num_sms() ? tiles : num_sms();
     if (K <= 256)  // HBM-bound: more stores in flight matter more than ring depth
         launch_k(k_gemm_tc<128, 256, false, 3, 4>, dim3(grid), dim3(NUM_THREADS), CfgHbm::SMEM_BYTES, st, tmA, *tmB, tmOut, bias, residual, out,

@@ -381,65 +381,68 @@ k_gemm_simple(const T *__restrict__ A, const T *__restrict__ Wkn, const float *_
 }
 
 // ---------------------------------------------------------------------------------------------------
-// K7 + head: GlobalAveragePooling2D -> [Dense(N1)+bias, ReLU] -> Dense(N2)+bias.  One CTA per image.
-// (N1 == 0 means the head is a single Dense(C -> N2).)  Warp-level reductions; 0.002 % of the MACs.
+// K7 + head: GlobalAveragePooling2D -> [Dense(N1)+bias, ReLU] -> Dense(N2)+bias, in two kernels so that a single image still
+// spreads over 16 CTAs (batch-1 latency) and a large batch does not re-read the dense kernel once per image row-by-row:
+//   k_gap_partial : CTA (slice s, image b): mean over H*W of channels [128 s, 128 s + 128) (warps split the pixels, shuffle-free
+//                   smem reduction), then the slice's contribution to every first-dense output -> partial[b][s][*]
+//   k_head_finish : CTA per image: fixed-order sum of the 16 partials (deterministic), +bias, ReLU, second dense (warp reductions)
+// (N1 == 0 means the head is a single Dense(C -> N2): the partials are then the logits' partial sums.)
 // ---------------------------------------------------------------------------------------------------
+constexpr int HEAD_SLICE = 128;   // channels per slice
+constexpr int HEAD_MAXN = 128;    // max width of the first dense layer
+
 template <typename T>
 __global__ void __launch_bounds__(256)
-k_gap_head(const T *__restrict__ in, int HW, int C, const float *__restrict__ W1, const float *__restrict__ b1,
-           int N1, const float *__restrict__ W2, const float *__restrict__ b2, int N2,
-           float *__restrict__ feat_out /*nullable [B,C]*/, float *__restrict__ logits) {
-    extern __shared__ float sm[];
-    float *feat = sm;            // [C]
-    float *part = sm + C;        // [8][128]
-    float *hid = part + 8 * 128; // [128]
-    const int b = blockIdx.x, tid = threadIdx.x;
+k_gap_partial(const T *__restrict__ in, int HW, int C, const float *__restrict__ Wd /*[C][Nd]*/, int Nd,
+              float *__restrict__ feat_out /*nullable [B,C]*/, float *__restrict__ partial /*[B][C/128][HEAD_MAXN]*/) {
+    __shared__ float4 red[8][32];
+    __shared__ float feat[HEAD_SLICE];
     pdl_launch_dependents();
     pdl_wait();
-    const T *base = in + (size_t)b * HW * C;
-    const float inv = 1.0f / (float)HW;
-    for (int c = tid * 4; c < C; c += blockDim.x * 4) {
-        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int p = 0; p < HW; ++p) s = add4(s, V4<T>::ld(base + (size_t)p * C + c));
-        feat[c] = s.x * inv; feat[c + 1] = s.y * inv; feat[c + 2] = s.z * inv; feat[c + 3] = s.w * inv;
-    }
-    __syncthreads();
-    if (feat_out)
-        for (int c = tid; c < C; c += blockDim.x) feat_out[(size_t)b * C + c] = feat[c];
+    const int s = blockIdx.x, b = blockIdx.y, tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
-    const int Nd = N1 > 0 ? N1 : N2;             // width of the first dense
-    const float *Wd = N1 > 0 ? W1 : W2;
-    // first dense: warp w takes k in its slice, lane handles outputs lane, lane+32, lane+64, lane+96
-    {
-        float a[4] = {0.f, 0.f, 0.f, 0.f};
-        int kper = (C + 7) / 8;
-        int k0 = warp * kper, k1 = min(C, k0 + kper);
-        for (int k = k0; k < k1; ++k) {
-            float f = feat[k];
+    const int nslices = C / HEAD_SLICE;
+    const T *base = in + (size_t)b * HW * C + (size_t)s * HEAD_SLICE + lane * 4;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int p = warp; p < HW; p += 8) acc = add4(acc, V4<T>::ld(base + (size_t)p * C));
+    red[warp][lane] = acc;
+    __syncthreads();
+    if (warp == 0) {
+        float4 t = red[0][lane];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                int n = lane + 32 * j;
-                if (n < Nd) a[j] = fmaf(f, __ldg(Wd + (size_t)k * Nd + n), a[j]);
-            }
-        }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) part[warp * 128 + lane + 32 * j] = a[j];
+        for (int w = 1; w < 8; ++w) t = add4(t, red[w][lane]);
+        const float inv = 1.0f / (float)HW;
+        feat[lane * 4 + 0] = t.x * inv; feat[lane * 4 + 1] = t.y * inv; feat[lane * 4 + 2] = t.z * inv; feat[lane * 4 + 3] = t.w * inv;
     }
     __syncthreads();
+    if (feat_out && tid < HEAD_SLICE) feat_out[(size_t)b * C + (size_t)s * HEAD_SLICE + tid] = feat[tid];
+    if (tid < Nd) {  // coalesced over the outputs: thread j walks the slice's 128 rows of the dense kernel
+        const float *w = Wd + (size_t)s * HEAD_SLICE * Nd + tid;
+        float a = 0.f;
+#pragma unroll 8
+        for (int k = 0; k < HEAD_SLICE; ++k) a = fmaf(feat[k], __ldg(w + (size_t)k * Nd), a);
+        partial[((size_t)b * nslices + s) * HEAD_MAXN + tid] = a;
+    }
+}
+
+__global__ void __launch_bounds__(128)
+k_head_finish(const float *__restrict__ partial, int nslices, const float *__restrict__ b1, int N1, const float *__restrict__ W2,
+              const float *__restrict__ b2, int N2, float *__restrict__ logits) {
+    __shared__ float hid[HEAD_MAXN];
+    pdl_launch_dependents();
+    pdl_wait();
+    const int b = blockIdx.x, tid = threadIdx.x;
+    const int Nd = N1 > 0 ? N1 : N2;
     if (tid < Nd) {
         float s = 0.f;
-#pragma unroll
-        for (int w = 0; w < 8; ++w) s += part[w * 128 + tid];
-        if (N1 > 0) {
-            hid[tid] = fmaxf(s + b1[tid], 0.f);
-        } else {
-            logits[(size_t)b * N2 + tid] = s + b2[tid];
-        }
+        for (int i = 0; i < nslices; ++i) s += partial[((size_t)b * nslices + i) * HEAD_MAXN + tid];  // fixed order
+        if (N1 > 0) hid[tid] = fmaxf(s + b1[tid], 0.f);
+        else logits[(size_t)b * N2 + tid] = s + b2[tid];
     }
     if (N1 == 0) return;
     __syncthreads();
-    // second dense: one warp per output, shuffle reduction
-    for (int n = warp; n < N2; n += 8) {
+    const int warp = tid >> 5, lane = tid & 31;
+    for (int n = warp; n < N2; n += 4) {
         float s = 0.f;
         for (int k = lane; k < N1; k += 32) s = fmaf(hid[k], __ldg(W2 + (size_t)k * N2 + n), s);
 #pragma unroll
