@@ -103,7 +103,8 @@ struct KdlModel {
     bool weights_loaded = false;
     bool no_fused_sepconv = false;   // KDL_NO_FUSED_SEPCONV=1: separate depthwise + pointwise kernels everywhere (A/B)
     int microbatch_mb = 0;           // KDL_MICROBATCH_MB: size (MiB) of the L2-resident depthwise->pointwise hand-off, 0 = off
-    bool use_pdl = false;            // KDL_PDL=1 enables programmatic dependent launch (measured: -2 % batch-1 latency, no throughput gain)
+    int pdl_max_batch = 64;          // programmatic dependent launch for forwards of at most this many images (launch-latency-bound
+                                     // regime: -9 % at batch 1, -5 % at 8, -1 % at 64; at 256 +0.4 % device but -1.5 % end to end); KDL_PDL=0 never, KDL_PDL=1 always
     bool conv_shifted_taps = false;  // KDL_CONV2_TAPS=1: 9 shifted TMA boxes per tile instead of the staged halo (A/B)
     int gemm_variant = 1;     // KDL_GEMM_VARIANT: tensor-bound layers use 1 = 128x256 single CTA, 2 = CTA pair (cta_group::2), 3 = 256x256 per CTA
     int launches = 0;
@@ -751,7 +752,8 @@ extern "C" int kdl_create(const KdlConfig *cfg, KdlModel **out) {
     }
     CKM(cudaStreamCreateWithFlags(&m->own_stream, cudaStreamNonBlocking));
     { const char *e1 = getenv("KDL_GEMM_VARIANT"); m->gemm_variant = e1 ? atoi(e1) : 1; }
-    { const char *e1 = getenv("KDL_PDL"); m->use_pdl = e1 && e1[0] == '1'; }
+    { const char *e1 = getenv("KDL_PDL"); if (e1 && e1[0] == '0') m->pdl_max_batch = 0; else if (e1 && e1[0] == '1') m->pdl_max_batch = 1 << 30; }
+    { const char *e1 = getenv("KDL_PDL_MAX_BATCH"); if (e1 && atoi(e1) >= 0 && e1[0]) m->pdl_max_batch = atoi(e1); }
     { const char *e1 = getenv("KDL_CONV2_TAPS"); m->conv_shifted_taps = e1 && e1[0] == '1'; }
     { const char *e1 = getenv("KDL_MICROBATCH_MB"); m->microbatch_mb = e1 ? atoi(e1) : 0; }
     { const char *e1 = getenv("KDL_NO_FUSED_SEPCONV"); m->no_fused_sepconv = e1 && e1[0] == '1'; }
@@ -856,7 +858,7 @@ static int run_forward_eager(KdlModel *m, const float *in_f32, const uint8_t *in
     struct PdlScope {  // programmatic dependent launch for the kernels of this forward pass (tensor-core path only)
         PdlScope(bool on) { pdl_enabled() = on; }
         ~PdlScope() { pdl_enabled() = false; }
-    } pdl_scope(m->use_pdl && m->cfg.precision == KDL_PRECISION_BF16 && m->cfg.gemm_impl == KDL_GEMM_AUTO && !m->profiling);
+    } pdl_scope(B <= m->pdl_max_batch && m->cfg.precision == KDL_PRECISION_BF16 && m->cfg.gemm_impl == KDL_GEMM_AUTO && !m->profiling);
     if (m->cfg.precision == KDL_PRECISION_F32) {
         Runner<float> r{m, st, B};
         return r.forward(in_f32, in_u8, d_logits);
