@@ -4,12 +4,12 @@ TF-Serving runs behind model_server.py:55.  Host code is Python calling a C-ABI 
 (include/kdl.h, csrc/); there is no CPU fallback."""
 from . import arch, weights  # noqa: F401
 
-__all__ = ["arch", "weights", "engine", "gateway", "replicas", "serving", "http_gateway"]
+__all__ = ["arch", "weights", "engine", "gateway", "replicas", "serving", "http_gateway", "batching", "hdf5_min", "keras_io"]
 
 
 def __getattr__(name):
     # engine / gateway / replicas import torch + the CUDA library: load lazily so that arch/weights stay light
-    if name in ("engine", "gateway", "replicas", "build", "_lib", "serving", "http_gateway"):
+    if name in ("engine", "gateway", "replicas", "build", "_lib", "serving", "http_gateway", "batching", "hdf5_min", "keras_io"):
         import importlib
         return importlib.import_module(f"{__name__}.{name}")
     raise AttributeError(name)

@@ -8,6 +8,8 @@ Same names, argument meaning and error behaviour as model_server.py for the hot 
 Image download + decode (urllib + PIL decoders inside keras-image-helper's from_url) stays on the CPU and is
 out of scope; inputs to the accelerated path are decoded RGB uint8 arrays.
 """
+import contextlib
+import threading
 from io import BytesIO
 from typing import Dict, List, Optional
 from urllib import request
@@ -35,7 +37,8 @@ class Preprocessor:
     """keras-image-helper 0.0.1 preprocessor surface (`from_url`, `from_path`, `resize_image`,
     `convert_to_tensor`), with resize + scaling executed by the fused CUDA kernel."""
 
-    def __init__(self, model: Model, target_size=(299, 299)):
+    def __init__(self, model: Model, target_size=(299, 299), lock=None):
+        self._lock = lock if lock is not None else contextlib.nullcontext()   # shared with whoever else drives `model`
         if tuple(target_size) != (model.input_size, model.input_size):
             raise ValueError(f"target_size {target_size} does not match the model's input size {model.input_size}")
         self.model = model
@@ -51,23 +54,28 @@ class Preprocessor:
 
     def from_array(self, rgb_u8: np.ndarray) -> np.ndarray:
         """decoded RGB uint8 HWC -> float32 (1,S,S,3) in [-1,1] (host array, like the reference returns)."""
-        return self.model.preprocess_uint8([rgb_u8]).cpu().numpy()
+        with self._lock:
+            return self.model.preprocess_uint8([rgb_u8]).cpu().numpy()
 
     def from_path(self, path: str) -> np.ndarray:
         with open(path, 'rb') as f:
             return self.from_array(self.decode(f.read()))
 
-    def from_url(self, url: str) -> np.ndarray:
+    def fetch(self, url: str) -> np.ndarray:
+        """download + decode -> RGB uint8 HWC (the CPU part of from_url)"""
         with request.urlopen(url) as resp:
             buffer = resp.read()
-        return self.from_array(self.decode(buffer))
+        return self.decode(buffer)
+
+    def from_url(self, url: str) -> np.ndarray:
+        return self.from_array(self.fetch(url))
 
 
-def create_preprocessor(name: str, target_size, model: Model) -> Preprocessor:
+def create_preprocessor(name: str, target_size, model: Model, lock=None) -> Preprocessor:
     """model_server.py:18 `create_preprocessor('xception', target_size=(299, 299))`."""
     if name != 'xception':
         raise ValueError(f"only the 'xception' preprocessing recipe is served here, got {name!r}")
-    return Preprocessor(model, target_size)
+    return Preprocessor(model, target_size, lock)
 
 
 def make_request(X: np.ndarray) -> dict:
@@ -85,9 +93,36 @@ def process_response(result: dict) -> Dict[str, float]:
 class Gateway:
     """Module-level state of model_server.py (stub + preprocessor) as an object."""
 
-    def __init__(self, model: Model):
+    def __init__(self, model: Model, batching=None):
+        """batching: a batching.BatchingParameters coalesces concurrent apply_model* calls (from the HTTP server's request
+        threads) into one forward call; None = one request at a time, the reference's single sync worker (gateway.dockerfile:17)."""
         self.model = model
-        self.preprocessor = create_preprocessor('xception', (model.input_size, model.input_size), model)
+        self._lock = threading.Lock()     # a KdlModel is not re-entrant
+        self.preprocessor = create_preprocessor('xception', (model.input_size, model.input_size), model, self._lock)
+        self._u8_batcher = self._f32_batcher = None
+        if batching is not None:
+            from .batching import DynamicBatcher
+            self._u8_batcher = DynamicBatcher(self._run_u8, batching)
+            self._f32_batcher = DynamicBatcher(self._run_f32, batching)
+
+    def _run_u8(self, images):
+        with self._lock:
+            return list(self.model.predict_uint8(list(images)))
+
+    def _run_f32(self, xs):
+        x = xs[0] if len(xs) == 1 else np.concatenate(xs, axis=0)
+        with self._lock:
+            y = self.model.serving_default(**{INPUT_KEY: x})[OUTPUT_KEY]
+        out, o = [], 0
+        for a in xs:
+            out.append(y[o:o + a.shape[0]])
+            o += a.shape[0]
+        return out
+
+    def close(self):
+        for b in (self._u8_batcher, self._f32_batcher):
+            if b is not None:
+                b.close()
 
     def Predict(self, pb_request: dict, timeout: Optional[float] = None) -> dict:
         spec = pb_request["model_spec"]
@@ -95,20 +130,34 @@ class Gateway:
             raise LookupError(f"Servable not found for request: Latest({spec['name']})")   # TF-Serving NOT_FOUND
         if spec["signature_name"] != SIGNATURE_NAME:
             raise LookupError(f"Serving signature key \"{spec['signature_name']}\" not found.")
-        return {"outputs": self.model.serving_default(**pb_request["inputs"])}
+        inputs = pb_request["inputs"]
+        if set(inputs) != {INPUT_KEY}:
+            raise ValueError(f"input tensor alias not found in signature: expected exactly {{{INPUT_KEY}}}, got {sorted(inputs)}")
+        x = inputs[INPUT_KEY]
+        if self._f32_batcher is not None and x.shape[0] > 0:
+            y = self._f32_batcher.submit(x, size=int(x.shape[0]), timeout=timeout)
+        else:
+            y = self._run_f32([x])[0]
+        return {"outputs": {OUTPUT_KEY: y}}
 
     def apply_model_array(self, rgb_u8: np.ndarray) -> Dict[str, float]:
         """apply_model on an already decoded image: fused uint8 path (resize+scale+Xception in one call)."""
-        logits = self.model.predict_uint8([rgb_u8])
-        return {c: float(p) for c, p in zip(labels, logits[0])}
+        if self._u8_batcher is not None:
+            row = self._u8_batcher.submit(rgb_u8)
+        else:
+            row = self._run_u8([rgb_u8])[0]
+        return {c: float(p) for c, p in zip(labels, row)}
 
     def apply_model(self, url: str) -> Dict[str, float]:
-        """model_server.py:52-56."""
+        """model_server.py:52-56.  With batching on, the decoded image goes straight to the fused uint8 path so that concurrent
+        requests share one resize+forward call (same logits: tests/test_gpu_gateway.py)."""
+        if self._u8_batcher is not None:
+            return self.apply_model_array(self.preprocessor.fetch(url))
         X = self.preprocessor.from_url(url)
         pb_request = make_request(X)
         pb_result = self.Predict(pb_request, timeout=20.0)
         return process_response(pb_result)
 
     def predict_batch(self, images: List[np.ndarray]) -> List[Dict[str, float]]:
-        logits = self.model.predict_uint8(images)
+        logits = self._run_u8(images)
         return [{c: float(p) for c, p in zip(labels, row)} for row in logits]

@@ -9,8 +9,12 @@ from http.server import BaseHTTPRequestHandler, ThreadingHTTPServer
 from typing import Callable, Dict
 
 
-def make_handler(apply_model: Callable[[str], Dict[str, float]]):
-    lock = threading.Lock()   # one request at a time reaches the model, like the single gunicorn sync worker (gateway.dockerfile:17)
+def make_handler(apply_model: Callable[[str], Dict[str, float]], concurrent: bool = False):
+    """concurrent=False: one request at a time reaches apply_model, like the single gunicorn sync worker (gateway.dockerfile:17).
+    concurrent=True: request threads call apply_model in parallel -- for a Gateway built with `batching`, which does its own
+    locking and coalesces the concurrent requests into one forward call."""
+    import contextlib
+    lock = contextlib.nullcontext() if concurrent else threading.Lock()
 
     class Handler(BaseHTTPRequestHandler):
         server_version = "kdl-gateway/0.1"
@@ -40,6 +44,8 @@ def make_handler(apply_model: Callable[[str], Dict[str, float]]):
             self._send(200, result)                        # jsonify(result)  (model_server.py:66)
 
         def do_GET(self):
+            if self.path.rstrip("/") == "/healthz":    # for readiness probes (deploy/); the reference has no health route
+                return self._send(200, {"status": "ok"})
             self._send(405, {"error": "method not allowed; POST /predict"})
 
         def log_message(self, fmt, *args):   # PYTHONUNBUFFERED-style stdout logging is the reference's only logging
@@ -48,14 +54,19 @@ def make_handler(apply_model: Callable[[str], Dict[str, float]]):
     return Handler
 
 
-def make_http_server(apply_model: Callable[[str], Dict[str, float]], host: str = "0.0.0.0", port: int = 9696) -> ThreadingHTTPServer:
-    return ThreadingHTTPServer((host, port), make_handler(apply_model))
+def make_http_server(apply_model: Callable[[str], Dict[str, float]], host: str = "0.0.0.0", port: int = 9696,
+                     concurrent: bool = False) -> ThreadingHTTPServer:
+    return ThreadingHTTPServer((host, port), make_handler(apply_model, concurrent))
 
 
 def main():   # pragma: no cover - process entry point
+    import os
     from . import engine, gateway, weights
-    model = engine.Model(weights.make_weights(1, "calibrated"), max_batch=32)
-    srv = make_http_server(gateway.Gateway(model).apply_model)
+    from .batching import BatchingParameters
+    model = engine.Model(weights.load_from_env(), max_batch=32)
+    batching = os.environ.get("KDL_ENABLE_BATCHING", "0") == "1"
+    params = BatchingParameters(32, int(os.environ.get("KDL_BATCH_TIMEOUT_MICROS", 1000))) if batching else None
+    srv = make_http_server(gateway.Gateway(model, batching=params).apply_model, concurrent=batching)
     print("gateway listening on 0.0.0.0:9696")
     srv.serve_forever()
 

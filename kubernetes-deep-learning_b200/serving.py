@@ -140,13 +140,35 @@ def tensor_proto_to_ndarray(p) -> np.ndarray:
 
 class PredictionServicer:
     """Implements Predict on top of any `serving_default(input_8=ndarray) -> {'dense_7': ndarray}` callable
-    (normally `engine.Model.serving_default`).  One request at a time reaches the model (a KdlModel is not re-entrant)."""
+    (normally `engine.Model.serving_default`).  One call at a time reaches the model (a KdlModel is not re-entrant): either one
+    request under a lock (the reference's configuration: TF-Serving without --enable_batching), or, with `batching`, one
+    coalesced batch of concurrent requests from the batcher's scheduler thread (batching.py)."""
 
-    def __init__(self, serving_default: Callable[..., Dict[str, np.ndarray]], input_size: int = 299, version: int = 1):
+    def __init__(self, serving_default: Callable[..., Dict[str, np.ndarray]], input_size: int = 299, version: int = 1,
+                 batching=None):
         self._fn = serving_default
         self._size = input_size
         self._version = version          # tf-serving.dockerfile:5 copies the model into version directory "1"
         self._lock = threading.Lock()
+        self.batcher = None
+        if batching is not None:
+            from .batching import DynamicBatcher
+            self.batcher = DynamicBatcher(self._run_batch, batching)
+
+    def _run_batch(self, xs):
+        """xs: list of (n_i, S, S, 3) float32 arrays -> list of (n_i, 10) arrays, one forward call for all of them."""
+        x = xs[0] if len(xs) == 1 else np.concatenate(xs, axis=0)
+        with self._lock:
+            y = np.asarray(self._fn(**{INPUT_KEY: x})[OUTPUT_KEY], dtype=np.float32)
+        out, o = [], 0
+        for a in xs:
+            out.append(y[o:o + a.shape[0]])
+            o += a.shape[0]
+        return out
+
+    def close(self):
+        if self.batcher is not None:
+            self.batcher.close()
 
     def Predict(self, request, context):
         import grpc
@@ -169,8 +191,14 @@ class PredictionServicer:
         if x.ndim != 4 or x.shape[1:] != (S, S, 3):
             context.abort(grpc.StatusCode.INVALID_ARGUMENT,
                           f"input_8 must have shape (-1,{S},{S},3) (guide.md:224), got {tuple(x.shape)}")
-        with self._lock:
-            y = np.asarray(self._fn(**{INPUT_KEY: x})[OUTPUT_KEY], dtype=np.float32)
+        if self.batcher is not None and x.shape[0] > 0:
+            from .batching import QueueFull
+            try:
+                y = self.batcher.submit(x, size=int(x.shape[0]))
+            except QueueFull as e:
+                context.abort(grpc.StatusCode.UNAVAILABLE, str(e))
+        else:
+            y = self._run_batch([x])[0]
         resp = PredictResponse()
         resp.model_spec.name = MODEL_NAME
         resp.model_spec.version.value = self._version
@@ -184,11 +212,15 @@ class PredictionServicer:
 
 
 def make_server(serving_default: Callable[..., Dict[str, np.ndarray]], address: str = "127.0.0.1:8500", input_size: int = 299,
-                max_workers: int = 4, max_message_mb: int = 512):
+                max_workers: int = 4, max_message_mb: int = 512, batching=None):
     """Returns (grpc.Server, bound_port).  Port 8500 is the one the reference's Service exposes
-    (tf-serving-clothing-model-service.yaml:9-10); pass ':0' for an ephemeral port."""
+    (tf-serving-clothing-model-service.yaml:9-10); pass ':0' for an ephemeral port.  `batching`: a
+    batching.BatchingParameters turns on server-side request coalescing (give the server at least max_batch_size workers:
+    every waiting request holds one)."""
     import grpc
-    servicer = PredictionServicer(serving_default, input_size)
+    servicer = PredictionServicer(serving_default, input_size, batching=batching)
+    if batching is not None:
+        max_workers = max(max_workers, 2 * batching.max_batch_size)
     handler = grpc.method_handlers_generic_handler(SERVICE, {
         "Predict": grpc.unary_unary_rpc_method_handler(servicer.Predict, request_deserializer=PredictRequest.FromString,
                                                        response_serializer=PredictResponse.SerializeToString)})
@@ -196,6 +228,7 @@ def make_server(serving_default: Callable[..., Dict[str, np.ndarray]], address: 
     server = grpc.server(futures.ThreadPoolExecutor(max_workers=max_workers), options=opts)
     server.add_generic_rpc_handlers((handler,))
     port = server.add_insecure_port(address)      # insecure, like the reference's channel (model_server.py:15)
+    server.kdl_servicer = servicer                # for servicer.batcher statistics and close()
     return server, port
 
 
@@ -208,12 +241,21 @@ class PredictionServiceStub:
 
 
 def serve_forever(weights=None, address: str = "0.0.0.0:8500", device: int = 0, max_batch: int = 32,
-                  model: Optional[object] = None):   # pragma: no cover - process entry point
-    """`python -m kdl_b200.serving`: the container entry point that replaces `tensorflow/serving:2.3.0` (tf-serving.dockerfile)."""
+                  model: Optional[object] = None, enable_batching: Optional[bool] = None):   # pragma: no cover - process entry point
+    """`python -m kdl_b200.serving`: the container entry point that replaces `tensorflow/serving:2.3.0` (tf-serving.dockerfile).
+    KDL_ENABLE_BATCHING=1 (or enable_batching=True) is the counterpart of TF-Serving's --enable_batching; KDL_BATCH_TIMEOUT_MICROS
+    and KDL_MAX_BATCH_SIZE set the two parameters that matter."""
+    import os
     from . import engine, weights as wmod
+    from .batching import BatchingParameters
+    if enable_batching is None:
+        enable_batching = os.environ.get("KDL_ENABLE_BATCHING", "0") == "1"
+    max_batch = int(os.environ.get("KDL_MAX_BATCH_SIZE", max_batch))
     if model is None:
-        model = engine.Model(weights or wmod.make_weights(1, "calibrated"), device=device, max_batch=max_batch)
-    server, port = make_server(model.serving_default, address, model.input_size)
+        model = engine.Model(weights or wmod.load_from_env(), device=device, max_batch=max_batch)
+    params = BatchingParameters(max_batch_size=max_batch,
+                                batch_timeout_micros=int(os.environ.get("KDL_BATCH_TIMEOUT_MICROS", 1000))) if enable_batching else None
+    server, port = make_server(model.serving_default, address, model.input_size, batching=params)
     server.start()
     print(f"PredictionService for '{MODEL_NAME}' listening on port {port}")
     server.wait_for_termination()

@@ -79,3 +79,26 @@ def unpack_blob(blob: np.ndarray, head_inner: int = 100) -> Dict[str, np.ndarray
     if off != blob.size:
         raise ValueError(f"blob has {blob.size} floats, spec needs {off}")
     return out
+
+
+def load(path: str) -> Dict[str, np.ndarray]:
+    """Weights from a file: Keras HDF5 (`.h5`/`.hdf5`/`.keras`-era whole-model or weights-only files) or `.npz` of
+    {variable name: array} (keras_io.py)."""
+    from . import keras_io
+    p = str(path).lower()
+    if p.endswith(".npz"):
+        return keras_io.load_keras_npz(path)
+    if p.endswith((".h5", ".hdf5")):
+        return keras_io.load_keras_h5(path)
+    raise ValueError(f"unknown weight file type: {path} (expected .h5, .hdf5 or .npz)")
+
+
+def load_from_env(default_seed: int = 1) -> Dict[str, np.ndarray]:
+    """$KDL_WEIGHTS names the weight file; without it the entry points serve the deterministic random-init bundle (the trained
+    file is a download link, guide.md:176) and say so."""
+    import os
+    path = os.environ.get("KDL_WEIGHTS")
+    if path:
+        return load(path)
+    print("KDL_WEIGHTS is not set: serving random-init weights (seed %d, 'calibrated')" % default_seed)
+    return make_weights(default_seed, "calibrated")

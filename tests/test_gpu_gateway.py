@@ -151,3 +151,34 @@ def test_unmodified_gateway_flow_over_grpc_and_http(gw, tmp_path):
         np.testing.assert_allclose(got, pred, rtol=0, atol=0)          # same engine, same logits as the gRPC path
     finally:
         srv.shutdown()
+
+
+def test_batched_gateway_gives_each_concurrent_request_its_own_unbatched_answer(gw):
+    """Gateway(batching=...) (request coalescing): 20 threads call apply_model_array at once with images of
+    different sizes; each must get bit-identical logits to the same image sent alone, and the model must have seen batches."""
+    import threading
+    from kdl_b200 import gateway
+    from kdl_b200.batching import BatchingParameters
+    g, _ = gw
+    rng = np.random.default_rng(21)
+    imgs = [rng.integers(0, 256, (int(rng.integers(64, 700)), int(rng.integers(64, 700)), 3), dtype=np.uint8) for _ in range(20)]
+    alone = [g.apply_model_array(im) for im in imgs]
+    gb = gateway.Gateway(g.model, batching=BatchingParameters(max_batch_size=min(8, g.model.max_batch), batch_timeout_micros=100000))
+    try:
+        got = [None] * len(imgs)
+
+        def work(i):
+            got[i] = gb.apply_model_array(imgs[i])
+        ts = [threading.Thread(target=work, args=(i,)) for i in range(len(imgs))]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join(60)
+        assert got == alone
+        assert max(gb._u8_batcher.batch_sizes) > 1 and gb._u8_batcher.images_run == len(imgs)
+        # the float path (Predict) is coalesced too
+        X = g.preprocessor.from_array(imgs[0])
+        y = gb.Predict(gateway.make_request(X), timeout=20.0)
+        assert gateway.process_response(y) == alone[0]
+    finally:
+        gb.close()

@@ -52,3 +52,22 @@ def test_error_statuses(base):
     with pytest.raises(urllib.error.HTTPError) as e:
         urllib.request.urlopen(base + "/predict", timeout=10)
     assert e.value.code == 405
+
+
+def test_health_route_for_probes(base):
+    with urllib.request.urlopen(base + "/healthz", timeout=10) as r:
+        assert r.status == 200 and json.loads(r.read()) == {"status": "ok"}
+
+
+def test_weight_file_dispatch(tmp_path, monkeypatch):
+    """KDL_WEIGHTS -> weights.load: Keras .h5 and .npz both give the bundle back; anything else is refused"""
+    import numpy as np
+    from kdl_b200 import keras_io, weights
+    W = weights.make_weights(2, "keras_default", head_inner=0)
+    p = tmp_path / "m.h5"
+    keras_io.export_keras_h5(W, str(p))
+    monkeypatch.setenv("KDL_WEIGHTS", str(p))
+    got = weights.load_from_env()
+    assert list(got) == list(W) and all(np.array_equal(got[k], W[k]) for k in W)
+    with pytest.raises(ValueError, match="unknown weight file type"):
+        weights.load(str(tmp_path / "m.ckpt"))

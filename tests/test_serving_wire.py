@@ -105,3 +105,44 @@ def test_errors_match_tf_serving_status_codes(stub):
     with pytest.raises(grpc.RpcError) as e:
         stub.Predict(make_request(np.zeros((1, 150, 150, 3), np.float32)), timeout=5.0)
     assert e.value.code() == grpc.StatusCode.INVALID_ARGUMENT
+
+
+def test_server_side_batching_coalesces_concurrent_requests_and_routes_rows_back():
+    """make_server(batching=...): 24 concurrent single-image Predict calls reach the model in fewer, larger calls, and every
+    client still receives the logits of its own image."""
+    import threading
+    from kdl_b200.batching import BatchingParameters
+    calls = []
+
+    def counting(**inputs):
+        calls.append(inputs["input_8"].shape[0])
+        return fake_serving_default(**inputs)
+    server, port = serving.make_server(counting, "127.0.0.1:0", input_size=8,
+                                       batching=BatchingParameters(max_batch_size=8, batch_timeout_micros=50000))
+    server.start()
+    try:
+        channel = grpc.insecure_channel(f"127.0.0.1:{port}")
+        stub = serving.PredictionServiceStub(channel)
+        rng = np.random.default_rng(5)
+        Xs = [rng.standard_normal((1, 8, 8, 3)).astype(np.float32) for _ in range(24)]
+        got = [None] * len(Xs)
+
+        def work(i):
+            got[i] = np.array(stub.Predict(make_request(Xs[i]), timeout=20.0).outputs['dense_7'].float_val, np.float32)
+        ts = [threading.Thread(target=work, args=(i,)) for i in range(len(Xs))]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join(30)
+        for X, g in zip(Xs, got):
+            np.testing.assert_array_equal(g, fake_serving_default(input_8=X)["dense_7"][0])
+        assert sum(calls) == 24 and max(calls) <= 8 and len(calls) < 24
+        # a multi-image request keeps its rows together
+        X3 = np.concatenate(Xs[:3], 0)
+        r = stub.Predict(make_request(X3), timeout=20.0).outputs['dense_7']
+        assert [d.size for d in r.tensor_shape.dim] == [3, 10]
+        np.testing.assert_array_equal(np.array(r.float_val, np.float32).reshape(3, 10), fake_serving_default(input_8=X3)["dense_7"])
+        channel.close()
+    finally:
+        server.stop(0)
+        server.kdl_servicer.close()
