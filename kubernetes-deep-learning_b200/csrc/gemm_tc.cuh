@@ -142,6 +142,9 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
 
+__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap *tm, int c0, int c1) {
+    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(tm), "r"(c0), "r"(c1) : "memory");
+}
 __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *tm, uint32_t bar, int c0, int c1) {
     asm volatile(
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
@@ -228,6 +231,11 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint4 v) {
     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
+__device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
 __device__ __forceinline__ float4 ld_shared_f4(uint32_t addr) {
     float4 v;
     asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
@@ -274,8 +282,9 @@ __device__ __forceinline__ uint4 epi8(const uint32_t *acc, uint32_t bias_addr, i
 template <int SW, int BN, bool CONV, int NST = (CONV ? 12 : 4), int EB = 2>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-          const __grid_constant__ CUtensorMap tmOut, const float *__restrict__ bias, const bf16 *residual, bf16 *out, int M,
-          int N, int K, int relu, ConvGeom cg, int ldo /*row pitch of out / residual in elements*/) {
+          const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes /*residual, box 64 x 128; L2 prefetch only*/,
+          const float *__restrict__ bias, const bf16 *residual, bf16 *out, int M, int N, int K, int relu, ConvGeom cg,
+          int ldo /*row pitch of out / residual in elements*/) {
     typedef Cfg<SW, BN, CONV, NST, EB> C;
     constexpr int STAGES = C::STAGES;
     constexpr int BK = C::BLOCK_K;
@@ -329,6 +338,13 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             }
             for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
                 const int m0 = (tile / n_tiles) * BLOCK_M, n0 = (tile % n_tiles) * BN;
+                if (!CONV && residual != nullptr) {
+                    // pull this tile's residual block into L2 now: the epilogue reads it ~one tile (several us) from now with plain
+                    // loads one 64-column chunk ahead, which hides an L2 hit but not an HBM miss (measured: +30 us per launch)
+#pragma unroll
+                    for (int c = 0; c < BN / 64; ++c)
+                        if (n0 + c * 64 < N) tma_prefetch_2d(&tmRes, n0 + c * 64, m0);
+                }
                 for (int kb = 0; kb < k_blocks; ++kb) {
                     mbar_wait(empty_bar(stage), phase ^ 1u);
                     mbar_expect_tx(full_bar(stage), C::STAGE_BYTES);
@@ -442,35 +458,53 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
                         *reinterpret_cast<uint4 *>(o + g * 8) = epi8(r + g * 8, bias_base + 32u * g, relu, false, make_uint4(0, 0, 0, 0));
                 }
             } else {
-                // ---- standard: 64-column chunks -> swizzled smem -> TMA store; residual prefetched a chunk ahead ----
-                const bool row_ok = row < M;
-                const bf16 *res_row = residual + (size_t)row * ldo;
+                // ---- standard: 64-column chunks -> swizzled smem -> TMA store ----
+                // Residual: a lane owns one output ROW, so loading its row directly would touch 32 cache lines per instruction.
+                // Instead the warp loads the 32 x 128-byte residual chunk coalesced (instruction g covers rows 4g..4g+3, eight lanes
+                // per row), one chunk ahead in registers, transposes it through the chunk's staging buffer (same swizzle as the
+                // output) and each lane then reads back its own row.
+                const int rl_row = row0 + (lane >> 3);                       // row of this lane in coalesced instruction 0
+                const bf16 *res_lane = has_res ? residual + (size_t)rl_row * ldo + (lane & 7) * 8 : nullptr;
                 uint4 rn[8];
                 auto load_res = [&](int c) {
+                    const int n = n0 + c * 64 + (lane & 7) * 8;
 #pragma unroll
-                    for (int g = 0; g < 8; ++g) {
-                        const int n = n0 + c * 64 + g * 8;
-                        rn[g] = (has_res && row_ok && n < N) ? *reinterpret_cast<const uint4 *>(res_row + n) : make_uint4(0, 0, 0, 0);
-                    }
+                    for (int g = 0; g < 8; ++g)
+                        rn[g] = (rl_row + 4 * g < M && n < N) ? *reinterpret_cast<const uint4 *>(res_lane + (size_t)(4 * g) * ldo + n0 + c * 64)
+                                                             : make_uint4(0, 0, 0, 0);
                 };
                 if (has_res) load_res(0);
                 mbar_wait(tfull_bar(acc), acc_phase);
                 tc_fence_after();
+#ifndef KDL_ABLATE_EPI
+#define KDL_ABLATE_EPI 0     // measurement builds only: 1 = no epilogue work at all, 2 = everything but the TMA stores
+#endif
 #pragma unroll
                 for (int c = 0; c < BN / 64; ++c) {
                     const int nc = n0 + c * 64;
-                    if (nc < N) {  // warp-uniform
+                    if (nc < N && KDL_ABLATE_EPI != 1) {  // warp-uniform
                         uint32_t r[64];
                         tmem_ld32(t_row + c * 64, r);
                         tmem_ld32(t_row + c * 64 + 32, r + 32);
-                        uint4 rc[8];
-#pragma unroll
-                        for (int g = 0; g < 8; ++g) rc[g] = rn[g];
-                        if (has_res && c + 1 < BN / 64 && nc + 64 < N) load_res(c + 1);
                         const uint32_t buf = ebuf + (uint32_t)(chunk_no++ % C::EPI_BUFS) * 4096u;  // ring over ALL chunks of all tiles
-                        // the TMA store issued two chunks ago from this buffer must have finished reading it
+                        // the TMA store issued EPI_BUFS chunks ago from this buffer must have finished reading it
                         if (lane == 0) bulk_wait_read<C::EPI_BUFS - 1>();
                         __syncwarp();
+                        uint4 rc[8];
+                        if (has_res) {
+#pragma unroll
+                            for (int g = 0; g < 8; ++g) {
+                                const uint32_t rr = (uint32_t)(4 * g + (lane >> 3));
+                                st_shared_v4(buf + rr * 128u + ((((uint32_t)lane & 7u) ^ (rr & 7u)) << 4), rn[g]);
+                            }
+                            __syncwarp();
+#pragma unroll
+                            for (int g = 0; g < 8; ++g) rc[g] = ld_shared_v4(buf + (uint32_t)lane * 128u + (uint32_t)((g ^ (lane & 7)) << 4));
+                            if (c + 1 < BN / 64 && nc + 64 < N) load_res(c + 1);
+                        } else {
+#pragma unroll
+                            for (int g = 0; g < 8; ++g) rc[g] = make_uint4(0, 0, 0, 0);
+                        }
                         tmem_ld_wait();
 #pragma unroll
                         for (int g = 0; g < 8; ++g) {
@@ -479,7 +513,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
                         }
                         fence_proxy_async_smem();
                         __syncwarp();
-                        if (lane == 0 && row0 < M) {
+                        if (lane == 0 && row0 < M && KDL_ABLATE_EPI != 2) {
                             tma_store_2d(&tmOut, buf, nc, row0);
                             bulk_commit();
                         }
@@ -531,6 +565,9 @@ inline int num_sms() {
 }
 
 // standard GEMM: A [M,K] bf16 row-major, weights via tmB (box BLOCK_K x BLOCK_N over Wt[N,K]), out [M,N]
+#ifndef KDL_HBM_CFG_MAX_K
+#define KDL_HBM_CFG_MAX_K 256
+#endif
 // lda / ldo: row pitch (elements) of A and of out/residual; 0 = dense (K / N)
 // tmB64 (optional): the same weights with a 64-row box; used when the 128x256 tiling would leave most SMs idle (small M)
 inline int launch_gemm(const TmaEncoder &enc, const bf16 *A, const CUtensorMap *tmB, const float *bias, const bf16 *residual,
@@ -538,17 +575,22 @@ inline int launch_gemm(const TmaEncoder &enc, const bf16 *A, const CUtensorMap *
                        const CUtensorMap *tmB64 = nullptr) {
     if (lda == 0) lda = K;
     if (ldo == 0) ldo = N;
-    CUtensorMap tmA, tmOut;
+    CUtensorMap tmA, tmOut, tmRes;
     if (!enc.encode_2d(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, BLOCK_K, BLOCK_M, 128) ||
         !enc.encode_2d(&tmOut, out, (uint64_t)N, (uint64_t)M, (uint64_t)ldo * 2, 64, 32, 128)) {
         snprintf(err, 512, "cuTensorMapEncodeTiled failed for A [%d,%d] / out [%d,%d]", M, K, M, N);
+        return KDL_ECUDA;
+    }
+    if (residual == nullptr) tmRes = tmOut;   // never dereferenced
+    else if (!enc.encode_2d(&tmRes, residual, (uint64_t)N, (uint64_t)M, (uint64_t)ldo * 2, 64, BLOCK_M, 128)) {
+        snprintf(err, 512, "cuTensorMapEncodeTiled failed for the residual [%d,%d]", M, N);
         return KDL_ECUDA;
     }
     const int tiles = ((M + BLOCK_M - 1) / BLOCK_M) * ((N + BLOCK_N - 1) / BLOCK_N);
     if (tmB64 && tiles * 2 < num_sms()) {
         const int tiles64 = ((M + BLOCK_M - 1) / BLOCK_M) * ((N + 63) / 64);
         const int grid64 = tiles64 < num_sms() ? tiles64 : num_sms();
-        launch_k(k_gemm_tc<128, 64, false, 4, 2>, dim3(grid64), dim3(NUM_THREADS), CfgSmallM::SMEM_BYTES, st, tmA, *tmB64, tmOut, bias, residual,
+        launch_k(k_gemm_tc<128, 64, false, 4, 2>, dim3(grid64), dim3(NUM_THREADS), CfgSmallM::SMEM_BYTES, st, tmA, *tmB64, tmOut, tmRes, bias, residual,
                  out, M, N, K, relu, ConvGeom{0, 0, 0, 0}, ldo);
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) {
@@ -558,11 +600,11 @@ inline int launch_gemm(const TmaEncoder &enc, const bf16 *A, const CUtensorMap *
         return KDL_OK;
     }
     const int grid = tiles < num_sms() ? tiles : num_sms();
-    if (K <= 256)  // HBM-bound: more stores in flight matter more than ring depth
-        launch_k(k_gemm_tc<128, 256, false, 3, 4>, dim3(grid), dim3(NUM_THREADS), CfgHbm::SMEM_BYTES, st, tmA, *tmB, tmOut, bias, residual, out,
+    if (K <= KDL_HBM_CFG_MAX_K)  // HBM-bound: more stores in flight matter more than ring depth
+        launch_k(k_gemm_tc<128, 256, false, 3, 4>, dim3(grid), dim3(NUM_THREADS), CfgHbm::SMEM_BYTES, st, tmA, *tmB, tmOut, tmRes, bias, residual, out,
                  M, N, K, relu, ConvGeom{0, 0, 0, 0}, ldo);
     else
-        launch_k(k_gemm_tc<128, 256, false>, dim3(grid), dim3(NUM_THREADS), CfgStd::SMEM_BYTES, st, tmA, *tmB, tmOut, bias, residual, out, M, N,
+        launch_k(k_gemm_tc<128, 256, false>, dim3(grid), dim3(NUM_THREADS), CfgStd::SMEM_BYTES, st, tmA, *tmB, tmOut, tmRes, bias, residual, out, M, N,
                  K, relu, ConvGeom{0, 0, 0, 0}, ldo);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
@@ -585,7 +627,7 @@ inline int launch_conv3x3(const TmaEncoder &enc, const bf16 *in, const CUtensorM
     }
     const int tiles = (M + BLOCK_M - 1) / BLOCK_M;
     const int grid = tiles < num_sms() ? tiles : num_sms();
-    k_gemm_tc<64, 64, true><<<grid, NUM_THREADS, CfgConv::SMEM_BYTES, st>>>(tmA, *tmB, tmA /*unused*/, bias, nullptr, out, M, Cout,
+    k_gemm_tc<64, 64, true><<<grid, NUM_THREADS, CfgConv::SMEM_BYTES, st>>>(tmA, *tmB, tmA /*unused*/, tmA /*unused*/, bias, nullptr, out, M, Cout,
                                                                             9 * Cin, relu, ConvGeom{Hin, Win, Hin - 2, Win - 2}, Cout);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
