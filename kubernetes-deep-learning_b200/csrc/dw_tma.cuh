@@ -81,7 +81,11 @@ __device__ __forceinline__ void bulk_load_1d(uint32_t dst, const void *src, uint
                  "r"(bytes), "r"(bar)
                  : "memory");
 }
-__device__ __forceinline__ float2 fmul2(float2 a, float2 b) { return make_float2(a.x * b.x, a.y * b.y); }
+__device__ __forceinline__ float2 fmul2(float2 a, float2 b) {  // packed fp32 multiply (FMUL2): same rounding as two scalar multiplies
+    unsigned long long d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(*reinterpret_cast<unsigned long long *>(&a)), "l"(*reinterpret_cast<unsigned long long *>(&b)));
+    return *reinterpret_cast<float2 *>(&d);
+}
 
 // streaming (evict-first) 8-byte store: the output is far larger than L2 and is next read by another kernel
 __device__ __forceinline__ void st_stream(bf16 *p, uint2 v) {

@@ -64,7 +64,74 @@ __global__ void __launch_bounds__(64, 1) k_probe(const __grid_constant__ CUtenso
     if (threadIdx.x == 0) cycles[blockIdx.x] = (unsigned long long)(clock64() - t0);
 }
 
+
+// GEMM-stage pattern: each ring stage receives an A box (128 rows of the big activation matrix) and a B box (256 rows of the small,
+// L2-resident weight matrix), either as two 2-D boxes of one 64-element K atom (what k_gemm_tc does) or as two 3-D boxes covering
+// KA consecutive K atoms (fewer, larger TMA operations for the same bytes).
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *tm, uint32_t bar, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(dst),
+                 "l"(tm), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+                 : "memory");
+}
+__global__ void __launch_bounds__(64, 1) k_probe_gemm(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                                                      int ring, int KA, int kblocks, int m_blocks, int tiles_per_cta, unsigned long long *cycles) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (tc::smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t a_bytes = 128u * 128u * KA, b_bytes = 256u * 128u * KA, stage_bytes = a_bytes + b_bytes;
+    const uint32_t bar = base + ring * stage_bytes;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < ring; ++s) { tc::mbar_init(bar + 8 * s, 1); tc::mbar_init(bar + 8 * (8 + s), 1); }
+        tc::fence_barrier_init();
+    }
+    __syncthreads();
+    const long long t0 = clock64();
+    const int steps = kblocks / KA;
+    if (threadIdx.x == 0) {
+        int stage = 0; uint32_t ph = 0;
+        for (int i = 0; i < tiles_per_cta; ++i) {
+            const int tile = blockIdx.x + i * gridDim.x;
+            const int mb = (tile / 3) % m_blocks, nb = tile % 3;
+            for (int k = 0; k < steps; ++k) {
+                tc::mbar_wait(bar + 8 * (8 + stage), ph ^ 1u);
+                tc::mbar_expect_tx(bar + 8 * stage, stage_bytes);
+                const uint32_t sa = base + stage * stage_bytes;
+                if (KA == 1) {
+                    tc::tma_load_2d(sa, &tmA, bar + 8 * stage, k * 64, mb * 128);
+                    tc::tma_load_2d(sa + a_bytes, &tmB, bar + 8 * stage, k * 64, nb * 256);
+                } else {
+                    tma_load_3d(sa, &tmA, bar + 8 * stage, 0, mb * 128, k * KA);
+                    tma_load_3d(sa + a_bytes, &tmB, bar + 8 * stage, 0, nb * 256, k * KA);
+                }
+                if (++stage == ring) { stage = 0; ph ^= 1u; }
+            }
+        }
+    } else if (threadIdx.x == 32) {
+        int stage = 0; uint32_t ph = 0;
+        for (int i = 0; i < tiles_per_cta * steps; ++i) {
+            tc::mbar_wait(bar + 8 * stage, ph);
+            tc::mbar_arrive(bar + 8 * (8 + stage));
+            if (++stage == ring) { stage = 0; ph ^= 1u; }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) cycles[blockIdx.x] = (unsigned long long)(clock64() - t0);
+}
+
 static tc::TmaEncoder enc;
+
+static CUtensorMap map3d_k(void *p, uint64_t rows, uint64_t pitch_bytes, int katoms_total, int box_rows, int KA) {
+    // (64 elements, rows, K atoms): atom stride 128 bytes
+    CUtensorMap tm;
+    cuuint64_t dims[3] = {64, rows, (cuuint64_t)katoms_total};
+    cuuint64_t strides[2] = {pitch_bytes, 128};
+    cuuint32_t box[3] = {64, (cuuint32_t)box_rows, (cuuint32_t)KA};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc.fn(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, p, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { printf("encode 3d failed (%d)\n", (int)r); exit(1); }
+    return tm;
+}
+
 
 static void run(const char *name, const CUtensorMap &tm, Job j, int rows_per_box, double valid_frac) {
     unsigned long long *d_cyc;
@@ -128,10 +195,11 @@ int main(int argc, char **argv) {
     void *p;
     cudaMalloc(&p, n * 2);
     cudaMemset(p, 0, n * 2);
-    const int per = 12 * B / 148;   // boxes per CTA: one pass over the tensor for the 64-channel boxes
+    const int reps = argc > 2 ? atoi(argv[2]) : 1;   // passes over the tensor (use > 1 with a small B for L2-resident rates)
+    const int per = 12 * B / 148 * reps;   // boxes per CTA: one pass over the tensor for the 64-channel boxes
     {   // GEMM A operand: [M = B*H*W, K = 768], box 64 x 128
         Job j{}; j.mode = 0; j.boxes_per_cta = per; j.box_rows = 128; j.box_cols = 64; j.box_bytes = 128 * 128;
-        j.n_colchunk = 12; j.n_rowblk = B * H * W / 128; j.boxes_per_cta = 12 * (B * H * W / 128) / 148;
+        j.n_colchunk = 12; j.n_rowblk = B * H * W / 128; j.boxes_per_cta = 12 * (B * H * W / 128) / 148 * reps;
         run("2-D  64ch x 128 rows  SWIZZLE_128B (GEMM A operand)", map2d(p, 768, (uint64_t)B * H * W, LD * 2, 64, 128, CU_TENSOR_MAP_SWIZZLE_128B), j, 128, 1.0);
         run("2-D  64ch x 128 rows  SWIZZLE_NONE", map2d(p, 768, (uint64_t)B * H * W, LD * 2, 64, 128, CU_TENSOR_MAP_SWIZZLE_NONE), j, 128, 1.0);
         Job k = j; k.box_rows = 256; k.box_bytes = 256 * 128; k.n_rowblk = B * H * W / 256; k.boxes_per_cta = j.boxes_per_cta / 2;
@@ -160,6 +228,37 @@ int main(int argc, char **argv) {
         Job j{}; j.mode = 1; j.boxes_per_cta = per; j.nch = 12; j.B = B / 4; j.chunk_elems = 64; j.x0 = 7; j.y0 = 7; j.box_bytes = 18 * 10 * 128;
         run("4-D  64ch x 18 x 10  SWIZZLE_NONE  interior (fused sepconv)", map4d(p, 728, 37, 37, B / 4, LD, 64, 18, 10, CU_TENSOR_MAP_SWIZZLE_NONE), j, 180, 1.0);
         run("4-D  64ch x 18 x 10  SWIZZLE_128B  interior", map4d(p, 728, 37, 37, B / 4, LD, 64, 18, 10, CU_TENSOR_MAP_SWIZZLE_128B), j, 180, 1.0);
+    }
+    {   // GEMM stage pattern, M = B*361 rows, K = 768 (12 atoms), N = 768
+        const int M = B * H * W, m_blocks = M / 128;
+        void *w; cudaMalloc(&w, 768 * 768 * 2); cudaMemset(w, 0, 768 * 768 * 2);
+        unsigned long long *d_cyc; cudaMalloc(&d_cyc, 148 * 8);
+        const int tiles_per_cta = m_blocks * 3 / 148;
+        for (int cfg = 0; cfg < 5; ++cfg) {
+            const int KA = cfg == 0 ? 1 : cfg <= 2 ? 2 : cfg == 3 ? 4 : 3, ring = cfg == 0 ? 4 : cfg == 1 ? 2 : cfg == 2 ? 2 : 1, dummy = 0; (void)dummy;
+            if (KA == 4 || KA == 3) { if (48 * 1024 * KA * ring > 220 * 1024) { } }
+            const uint32_t smem = ring * 48u * 1024u * KA + 1024 + 256;
+            if (smem > 227u * 1024u) { printf("cfg %d skipped (smem)\n", cfg); continue; }
+            CUtensorMap tmA = KA == 1 ? map2d(p, 768, (uint64_t)M, LD * 2, 64, 128, CU_TENSOR_MAP_SWIZZLE_128B) : map3d_k(p, (uint64_t)M, LD * 2, 12, 128, KA);
+            CUtensorMap tmB = KA == 1 ? map2d(w, 768, 768, 768 * 2, 64, 256, CU_TENSOR_MAP_SWIZZLE_128B) : map3d_k(w, 768, 768 * 2, 12, 256, KA);
+            cudaFuncSetAttribute(k_probe_gemm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+            float best = 1e30f;
+            for (int rep = 0; rep < 3; ++rep) {
+                cudaEventRecord(e0);
+                k_probe_gemm<<<148, 64, smem>>>(tmA, tmB, ring, KA, 12, m_blocks, tiles_per_cta, d_cyc);
+                cudaEventRecord(e1);
+                cudaError_t e = cudaDeviceSynchronize();
+                if (e != cudaSuccess) { printf("gemm probe cfg %d FAILED: %s\n", cfg, cudaGetErrorString(e)); exit(1); }
+                float ms; cudaEventElapsedTime(&ms, e0, e1);
+                if (rep && ms < best) best = ms;
+            }
+            const double bytes = 148.0 * tiles_per_cta * 12 * 48.0 * 1024;
+            const double flops = 148.0 * tiles_per_cta * 2.0 * 128 * 256 * 768;
+            printf("GEMM operand feed: %d K-atoms per TMA box, ring %d (%3u KB in flight): %7.3f ms  %7.1f GB/s = %5.1f B/clk/SM @1.85GHz  -> feeds %6.0f TFLOP/s\n",
+                   KA, ring, ring * 48u * KA, best, bytes / best * 1e-6, bytes / best * 1e-6 / 148 / 1.85, flops / best * 1e-9);
+        }
+        cudaFree(w); cudaFree(d_cyc);
     }
     cudaFree(p);
     return 0;
