@@ -104,6 +104,8 @@ def cpu_reference_rate(n_images, size, steps=1, warmup=0, seed=1234):
     from kdl_b200 import weights
     from oracle import preprocess_oracle as po
     from oracle import xception_oracle as xo
+    # torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU arm is meant to use all the host threads it can
+    torch.set_num_threads(max(1, len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)))
     W = weights.make_weights(1, "calibrated")
     imgs = synth_images(n_images, size, seed)
     times = []
@@ -129,6 +131,11 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "kdl" else args.warmup
+    # The contract is ONE JSON line on stdout.  Libraries print there too (NCCL's version banner comes from C code), so file
+    # descriptor 1 is pointed at stderr for the whole run and the line goes to a private copy of the real stdout.
+    sys.stdout.flush()
+    json_out = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
 
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -152,7 +159,7 @@ def main():
             "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
         }
-        print(json.dumps(line))
+        print(json.dumps(line), file=json_out, flush=True)
         return
 
     # ------------------------------------------------------------------ kdl arm (GPU)
@@ -313,7 +320,7 @@ def main():
                                 "host_cpus": os.cpu_count()}
     model.close()
     if rank == 0:
-        print(json.dumps(line))
+        print(json.dumps(line), file=json_out, flush=True)
     if dist is not None:
         dist.destroy_process_group()
 
