@@ -36,13 +36,14 @@ struct Params {
     int NS, RS;      // row strips per tile and rows per strip
     int ntx, nty, nch, total_tiles;
     int relu_in;
+    int rev;         // 1: walk the tiles from the last to the first (the consumer of a tensor larger than L2 starts where its producer stopped)
     uint32_t tile_bytes, stage_bytes;
     int consumer_threads;
 };
 
 inline Params make_params(int B, int H, int W, int C, int ld, int relu_in) {
     Params p;
-    p.B = B; p.H = H; p.W = W; p.C = C; p.ld = ld; p.relu_in = relu_in;
+    p.B = B; p.H = H; p.W = W; p.C = C; p.ld = ld; p.relu_in = relu_in; p.rev = 0;
     int ntx = (W + 19) / 20;                 // tiles <= 20 columns wide: 10 column pairs x 16 channel groups = 160 threads per strip
     p.TW = (W + ntx - 1) / ntx;
     p.ntx = ntx;
@@ -172,7 +173,8 @@ k_dw_tma(const __grid_constant__ CUtensorMap tmIn, const float *__restrict__ wpa
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
+            for (int ti = blockIdx.x; ti < p.total_tiles; ti += gridDim.x) {
+                const int t = p.rev ? p.total_tiles - 1 - ti : ti;
                 const int ch = t % p.nch;
                 int s = t / p.nch;
                 const int tx = s % p.ntx; s /= p.ntx;
@@ -198,7 +200,8 @@ k_dw_tma(const __grid_constant__ CUtensorMap tmIn, const float *__restrict__ wpa
     const bool active = strip < p.NS;
     int stage = 0;
     uint32_t phase = 0;
-    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
+    for (int ti = blockIdx.x; ti < p.total_tiles; ti += gridDim.x) {
+        const int t = p.rev ? p.total_tiles - 1 - ti : ti;
         const int ch = t % p.nch;
         int s = t / p.nch;
         const int tx = s % p.ntx; s /= p.ntx;
@@ -291,8 +294,9 @@ inline int configure(char *err) {
 }
 
 inline int launch(const tc::TmaEncoder &enc, const bf16 *in, const float *wpad, bf16 *out, int B, int H, int W, int C, int ld,
-                  int relu_in, cudaStream_t st, char *err) {
+                  int relu_in, cudaStream_t st, char *err, int rev = 0) {
     Params p = make_params(B, H, W, C, ld, relu_in);
+    p.rev = rev;
     CUtensorMap tm;
     if (!encode_input_map(enc, &tm, in, p)) {
         snprintf(err, 512, "cuTensorMapEncodeTiled(4d) failed for depthwise input [%d,%d,%d,%d] box [%d,%d]", B, H, W, C, p.BW, p.BH);

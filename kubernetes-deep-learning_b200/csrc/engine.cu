@@ -103,6 +103,7 @@ struct KdlModel {
     bool weights_loaded = false;
     bool no_fused_sepconv = false;   // KDL_NO_FUSED_SEPCONV=1: separate depthwise + pointwise kernels everywhere (A/B)
     int microbatch_mb = 0;           // KDL_MICROBATCH_MB: size (MiB) of the L2-resident depthwise->pointwise hand-off, 0 = off
+    bool serpentine = true;          // KDL_SERPENTINE=0 turns the alternating tile order off (A/B measurements)
     int pdl_max_batch = 64;          // programmatic dependent launch for forwards of at most this many images (launch-latency-bound
                                      // regime: -9 % at batch 1, -5 % at 8, -1 % at 64; at 256 +0.4 % device but -1.5 % end to end); KDL_PDL=0 never, KDL_PDL=1 always
     bool conv_shifted_taps = false;  // KDL_CONV2_TAPS=1: 9 shifted TMA boxes per tile instead of the staged halo (A/B)
@@ -225,6 +226,12 @@ template <typename T> struct Runner {
     KdlModel *m;
     cudaStream_t st;
     int B;
+    // Serpentine traversal: most activations are larger than the 126 MB L2, so a consumer that walks a tensor in the producer's
+    // order finds the start already evicted and thrashes (ncu: the pointwise GEMM re-read ALL of its input from DRAM).  A kernel
+    // that can walk its tiles backwards therefore runs opposite to the kernel before it: it starts on the freshest data.
+    int prev_rev = 0;
+    int flip() { prev_rev = m->serpentine ? 1 - prev_rev : 0; return prev_rev; }
+    void no_flip() { prev_rev = 0; }   // a kernel without a reverse mode ran forwards
 
     int alloc_tap(const char *name, int H, int C, int relu_applied, bool is_float, int *idx) {
         char *err = m->err;
@@ -262,7 +269,7 @@ template <typename T> struct Runner {
         dim3 grid((vec + 127) / 128, (H + rows - 1) / rows, B);
         prof_open(m, st, PC_DW, 18.0 * B * H * H * C, 2.0 * B * H * H * C * sizeof(T) + 36.0 * C, "dw H=%d C=%d relu=%d", H, C, relu_in);
         if (use_tc()) {
-            int rc = dwt::launch(m->tma, (const bf16 *)in, wpad, (bf16 *)out, B, H, H, C, ld(C), relu_in, st, m->err);
+            int rc = dwt::launch(m->tma, (const bf16 *)in, wpad, (bf16 *)out, B, H, H, C, ld(C), relu_in, st, m->err, flip());
             prof_close(m, st);
             if (rc != KDL_OK) return rc;
             m->launches++;
@@ -290,6 +297,7 @@ template <typename T> struct Runner {
         if (use_tc() && rm.mode == 0 && tc::shape_supported(M, g.N, g.K)) {
             prof_open(m, st, g.K >= 512 ? PC_PW_TC_TENSOR : PC_PW_TC_HBM, flops, bytes, "gemm M=%d N=%d K=%d", M, g.N, g.K);
             int rc;
+            if ((m->gemm_variant == 2 || m->gemm_variant == 3) && M >= 2048 && g.K >= 512) no_flip();
             if (m->gemm_variant == 3 && M >= 2048 && g.K >= 512)  // 256x256 tile per CTA (two M tiles share each weight block)
                 rc = tcm2::launch(m->tma, (const bf16 *)A, &g.tmB, g.bias, (const bf16 *)resid, (bf16 *)out, M, g.N, g.K, relu, st, m->err,
                                   ld(g.K), ld(g.N));
@@ -298,7 +306,7 @@ template <typename T> struct Runner {
                                        st, m->err, ld(g.K), ld(g.N));
             else
                 rc = tc::launch_gemm(m->tma, (const bf16 *)A, &g.tmB, g.bias, (const bf16 *)resid, (bf16 *)out,
-                                     M, g.N, g.K, relu, st, m->err, ld(g.K), ld(g.N), &g.tmB64);
+                                     M, g.N, g.K, relu, st, m->err, ld(g.K), ld(g.N), &g.tmB64, flip());
             prof_close(m, st);
             if (rc != KDL_OK) return rc;
             m->launches++;
@@ -343,6 +351,7 @@ template <typename T> struct Runner {
         const double px = (double)B * H * H;
         prof_open(m, st, PC_SEPFUSED, 2.0 * px * (9.0 * g.K + (double)g.K * g.N), (px * g.K + px * g.N + (double)g.K * g.N) * 2.0 + 36.0 * g.K,
                   "sepfused H=%d K=%d N=%d", H, g.K, g.N);
+        no_flip();
         int rc = sepc::launch(m->tma, (const bf16 *)in, m->dwpad[si], &g.tmB, g.bias, (bf16 *)out, B, H, H, g.K, g.N, ld(g.K), ld(g.N),
                               relu_in, relu_out, st, m->err);
         prof_close(m, st);
@@ -373,6 +382,7 @@ template <typename T> struct Runner {
         int pad_lo = pad_total / 2;  // TF SAME: extra padding goes to the end
         prof_open(m, st, PC_POOL, 0.0, ((double)B * H * H * C + 2.0 * B * Ho * Ho * C) * sizeof(T), "pool H=%d C=%d", H, C);
         if (use_tc()) {
+            no_flip();
             int rc = poolt::launch(m->tma, (const bf16 *)in, (const bf16 *)resid, (bf16 *)out, (bf16 *)sub, B, H, H, C, ld(C), Ho, Ho, pad_lo,
                                    st, m->err);
             prof_close(m, st);
@@ -753,6 +763,7 @@ extern "C" int kdl_create(const KdlConfig *cfg, KdlModel **out) {
     CKM(cudaStreamCreateWithFlags(&m->own_stream, cudaStreamNonBlocking));
     { const char *e1 = getenv("KDL_GEMM_VARIANT"); m->gemm_variant = e1 ? atoi(e1) : 1; }
     { const char *e1 = getenv("KDL_PDL"); if (e1 && e1[0] == '0') m->pdl_max_batch = 0; else if (e1 && e1[0] == '1') m->pdl_max_batch = 1 << 30; }
+    { const char *e1 = getenv("KDL_SERPENTINE"); if (e1 && e1[0] == '0') m->serpentine = false; }
     { const char *e1 = getenv("KDL_PDL_MAX_BATCH"); if (e1 && atoi(e1) >= 0 && e1[0]) m->pdl_max_batch = atoi(e1); }
     { const char *e1 = getenv("KDL_CONV2_TAPS"); m->conv_shifted_taps = e1 && e1[0] == '1'; }
     { const char *e1 = getenv("KDL_MICROBATCH_MB"); m->microbatch_mb = e1 ? atoi(e1) : 0; }

@@ -284,7 +284,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
           const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes /*residual, box 64 x 128; L2 prefetch only*/,
           const float *__restrict__ bias, const bf16 *residual, bf16 *out, int M, int N, int K, int relu, ConvGeom cg,
-          int ldo /*row pitch of out / residual in elements*/) {
+          int ldo /*row pitch of out / residual in elements*/, int rev = 0 /*1: walk the tiles from the last to the first*/) {
     typedef Cfg<SW, BN, CONV, NST, EB> C;
     constexpr int STAGES = C::STAGES;
     constexpr int BK = C::BLOCK_K;
@@ -336,7 +336,8 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
                 mbar_expect_tx(wres_bar, C::W_RES_BYTES);
                 for (int t = 0; t < 9; ++t) tma_load_2d(wres_base + t * (BN * SW), &tmB, wres_bar, t * BK, 0);
             }
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            for (int ti = blockIdx.x; ti < num_tiles; ti += gridDim.x) {
+                const int tile = rev ? num_tiles - 1 - ti : ti;
                 const int m0 = (tile / n_tiles) * BLOCK_M, n0 = (tile % n_tiles) * BN;
                 if (!CONV && residual != nullptr) {
                     // pull this tile's residual block into L2 now: the epilogue reads it ~one tile (several us) from now with plain
@@ -367,7 +368,8 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             uint32_t phase = 0;
             int it = 0;
             if (CONV) mbar_wait(wres_bar, 0);
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+            for (int ti = blockIdx.x; ti < num_tiles; ti += gridDim.x, ++it) {
+                const int tile = rev ? num_tiles - 1 - ti : ti;
                 const int n0 = (tile % n_tiles) * BN;
                 const int acc = it & 1;
                 const uint32_t acc_phase = (it >> 1) & 1;
@@ -405,7 +407,8 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         uint32_t chunk_no = 0;
         float bpre[(BN + 127) / 128];
         int it = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+        for (int ti = blockIdx.x; ti < num_tiles; ti += gridDim.x, ++it) {
+            const int tile = rev ? num_tiles - 1 - ti : ti;
             const int m0 = (tile / n_tiles) * BLOCK_M, n0 = (tile % n_tiles) * BN;
             const int acc = it & 1;
             const uint32_t acc_phase = (it >> 1) & 1;
@@ -425,8 +428,9 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
                 staged_n0 = n0;
             }
             {
-                const int next = tile + gridDim.x;
-                if (next < num_tiles) {
+                const int nti = ti + gridDim.x;
+                if (nti < num_tiles) {
+                    const int next = rev ? num_tiles - 1 - nti : nti;
                     const int nn0 = (next % n_tiles) * BN;
                     if (nn0 != staged_n0) {
 #pragma unroll
@@ -572,7 +576,7 @@ inline int num_sms() {
 // tmB64 (optional): the same weights with a 64-row box; used when the 128x256 tiling would leave most SMs idle (small M)
 inline int launch_gemm(const TmaEncoder &enc, const bf16 *A, const CUtensorMap *tmB, const float *bias, const bf16 *residual,
                        bf16 *out, int M, int N, int K, int relu, cudaStream_t st, char *err, int lda = 0, int ldo = 0,
-                       const CUtensorMap *tmB64 = nullptr) {
+                       const CUtensorMap *tmB64 = nullptr, int rev = 0) {
     if (lda == 0) lda = K;
     if (ldo == 0) ldo = N;
     CUtensorMap tmA, tmOut, tmRes;
@@ -591,7 +595,7 @@ inline int launch_gemm(const TmaEncoder &enc, const bf16 *A, const CUtensorMap *
         const int tiles64 = ((M + BLOCK_M - 1) / BLOCK_M) * ((N + 63) / 64);
         const int grid64 = tiles64 < num_sms() ? tiles64 : num_sms();
         launch_k(k_gemm_tc<128, 64, false, 4, 2>, dim3(grid64), dim3(NUM_THREADS), CfgSmallM::SMEM_BYTES, st, tmA, *tmB64, tmOut, tmRes, bias, residual,
-                 out, M, N, K, relu, ConvGeom{0, 0, 0, 0}, ldo);
+                 out, M, N, K, relu, ConvGeom{0, 0, 0, 0}, ldo, rev);
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) {
             snprintf(err, 512, "k_gemm_tc<small-M> launch (M=%d N=%d K=%d): %s", M, N, K, cudaGetErrorString(e));
@@ -602,10 +606,10 @@ inline int launch_gemm(const TmaEncoder &enc, const bf16 *A, const CUtensorMap *
     const int grid = tiles < num_sms() ? tiles : num_sms();
     if (K <= KDL_HBM_CFG_MAX_K)  // HBM-bound: more stores in flight matter more than ring depth
         launch_k(k_gemm_tc<128, 256, false, 3, 4>, dim3(grid), dim3(NUM_THREADS), CfgHbm::SMEM_BYTES, st, tmA, *tmB, tmOut, tmRes, bias, residual, out,
-                 M, N, K, relu, ConvGeom{0, 0, 0, 0}, ldo);
+                 M, N, K, relu, ConvGeom{0, 0, 0, 0}, ldo, rev);
     else
         launch_k(k_gemm_tc<128, 256, false>, dim3(grid), dim3(NUM_THREADS), CfgStd::SMEM_BYTES, st, tmA, *tmB, tmOut, tmRes, bias, residual, out, M, N,
-                 K, relu, ConvGeom{0, 0, 0, 0}, ldo);
+                 K, relu, ConvGeom{0, 0, 0, 0}, ldo, rev);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         snprintf(err, 512, "k_gemm_tc launch (M=%d N=%d K=%d): %s", M, N, K, cudaGetErrorString(e));
