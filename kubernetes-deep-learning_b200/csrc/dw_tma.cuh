@@ -254,6 +254,7 @@ k_dw_tma(const __grid_constant__ CUtensorMap tmIn, const float *__restrict__ wpa
             scatter_row<RELU, false, true, true>(rowaddr, wl, wh, aA, aB, aC);
             rotate();
             rowaddr += rowpitch;
+#pragma unroll 3
             for (int r = y_lo + 1; r < y_hi; ++r, rowaddr += rowpitch) {
                 scatter_row<RELU, true, true, true>(rowaddr, wl, wh, aA, aB, aC);
                 store_row();
