@@ -408,6 +408,8 @@ template <typename T> struct Runner {
         {
             long long threads = (long long)B * sp[1] * ((sp[1] + 1) / 2);  // one thread per pair of output pixels
             unsigned grid = (unsigned)((threads + 127) / 128);
+            const unsigned persistent = (unsigned)tc::num_sms() * 8;    // k_conv1 loops over pixel pairs (4 CTAs of 128 threads per SM, 2 waves)
+            if (grid > persistent) grid = persistent;
             prof_open(m, st, PC_CONV1, 2.0 * 27 * 32 * B * sp[1] * sp[1],
                       (double)B * sp[0] * sp[0] * 3 * (in_f32 ? 4 : 1) + (double)B * sp[1] * sp[1] * 32 * sizeof(T));
             if (in_f32) launch_k(k_conv1<float, T>, dim3(grid), dim3(128), 0, st, in_f32, m->w_conv1, m->b_conv1, U, B, sp[0], sp[1]);

@@ -117,9 +117,9 @@ k_conv1(const TIn *__restrict__ in, const float *__restrict__ w /*[27][32]*/, co
     pdl_launch_dependents();
     pdl_wait();
     const int Wp = (Ho + 1) >> 1;  // pixel pairs per output row
-    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const long long npairs = (long long)B * Ho * Wp;
-    if (t >= npairs) return;
+    // persistent: the 3.4 KB of weights and the LUT are staged once per CTA, not once per 256 output pixels
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < npairs; t += (long long)gridDim.x * blockDim.x) {
     const int b = (int)(t / ((long long)Ho * Wp));
     const int r = (int)(t - (long long)b * Ho * Wp);
     const int oy = r / Wp, ox = (r - oy * Wp) * 2;
@@ -161,6 +161,7 @@ k_conv1(const TIn *__restrict__ in, const float *__restrict__ w /*[27][32]*/, co
         for (int c = 0; c < 4; ++c)
             st8<T>(o + 32 + c * 8, relu4(make_float4(acc1[4 * c].x, acc1[4 * c].y, acc1[4 * c + 1].x, acc1[4 * c + 1].y)),
                    relu4(make_float4(acc1[4 * c + 2].x, acc1[4 * c + 2].y, acc1[4 * c + 3].x, acc1[4 * c + 3].y)));
+    }
     }
 }
 
