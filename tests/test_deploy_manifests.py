@@ -8,14 +8,16 @@ yaml = pytest.importorskip("yaml")
 D = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "deploy")
 
 
-def _load(name):
+def _load(name, kind):
     with open(os.path.join(D, name)) as f:
-        return yaml.safe_load(f)
+        docs = [d for d in yaml.safe_load_all(f) if d]
+    (doc,) = [d for d in docs if d["kind"] == kind]
+    return doc
 
 
 def test_model_server_deployment_and_service_keep_the_reference_contract():
-    dep = _load("tf-serving-clothing-model-deployment.yaml")
-    svc = _load("tf-serving-clothing-model-service.yaml")
+    dep = _load("kdl-model-server.yaml", "Deployment")
+    svc = _load("kdl-model-server.yaml", "Service")
     assert dep["kind"] == "Deployment" and dep["metadata"]["name"] == "tf-serving-clothing-model"
     c = dep["spec"]["template"]["spec"]["containers"][0]
     assert c["ports"] == [{"containerPort": 8500}]
@@ -28,8 +30,8 @@ def test_model_server_deployment_and_service_keep_the_reference_contract():
 
 
 def test_single_container_gateway_keeps_the_public_service():
-    dep = _load("serving-gateway-gpu-deployment.yaml")
-    svc = _load("serving-gateway-service.yaml")
+    dep = _load("kdl-gateway-inprocess.yaml", "Deployment")
+    svc = _load("kdl-gateway-inprocess.yaml", "Service")
     c = dep["spec"]["template"]["spec"]["containers"][0]
     assert c["ports"] == [{"containerPort": 9696}] and c["resources"]["limits"]["nvidia.com/gpu"] == 1
     assert c["readinessProbe"]["httpGet"] == {"path": "/healthz", "port": 9696}

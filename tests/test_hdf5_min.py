@@ -148,3 +148,45 @@ def test_errors_name_the_problem():
         h5.File(bytes(v2))
     with pytest.raises(h5.Hdf5Error, match="cannot write dtype"):
         h5.write_file(None, {"c": np.zeros(3, np.complex64)})
+
+
+def test_random_trees_round_trip():
+    """property test: any nested tree of float / int arrays with string attributes survives write -> read"""
+    hyp = pytest.importorskip("hypothesis")
+    st = pytest.importorskip("hypothesis.strategies")
+    hnp = pytest.importorskip("hypothesis.extra.numpy")
+    names = st.text(alphabet="abcdefghijklmnopqrstuvwxyz_0123456789:", min_size=1, max_size=12)
+    arrays = st.one_of(
+        hnp.arrays(np.float32, hnp.array_shapes(min_dims=0, max_dims=4, max_side=5), elements=st.floats(-1e6, 1e6, width=32)),
+        hnp.arrays(np.int64, hnp.array_shapes(min_dims=1, max_dims=2, max_side=6), elements=st.integers(-2**40, 2**40)),
+        hnp.arrays(np.uint8, hnp.array_shapes(min_dims=1, max_dims=3, max_side=4)))
+    trees = st.recursive(st.dictionaries(names, arrays, max_size=4),
+                         lambda children: st.dictionaries(names, st.one_of(arrays, children), max_size=4), max_leaves=12)
+
+    def flatten(t, prefix=""):
+        out = {}
+        for k, v in t.items():
+            if isinstance(v, dict):
+                out.update(flatten(v, prefix + "/" + k))
+            else:
+                out[prefix + "/" + k] = v
+        return out
+
+    @hyp.settings(max_examples=60, deadline=None)
+    @hyp.given(trees, st.lists(st.binary(min_size=1, max_size=9).filter(lambda b: b"\0" not in b), max_size=3))
+    def check(tree, strs):
+        if strs:
+            tree = dict(tree)
+            tree[".attrs"] = {"names": np.array(strs)}
+        blob = h5.write_file(None, tree)
+        f = h5.File(blob)
+        got = {k: n.read() for k, n in f.walk()}
+        want = flatten({k: v for k, v in tree.items() if k != ".attrs"})
+        assert sorted(got) == sorted(want)
+        for k in want:
+            assert got[k].dtype == want[k].dtype and got[k].shape == want[k].shape
+            np.testing.assert_array_equal(got[k], want[k])
+        if strs:
+            assert [bytes(x) for x in f.attrs["names"]] == strs
+
+    check()
