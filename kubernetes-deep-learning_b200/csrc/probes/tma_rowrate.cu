@@ -23,6 +23,7 @@ struct Job {
     int n_rowblk, n_colchunk, box_rows, box_cols;
     // 4-D
     int nch, B, x0, y0, chunk_elems;
+    const void *raw;   // mode 2: contiguous blocks of box_bytes
 };
 
 __global__ void __launch_bounds__(64, 1) k_probe(const __grid_constant__ CUtensorMap tm, Job j, unsigned long long *cycles) {
@@ -46,6 +47,9 @@ __global__ void __launch_bounds__(64, 1) k_probe(const __grid_constant__ CUtenso
             if (j.mode == 0) {
                 const int cc = (int)(t % j.n_colchunk), rb = (int)((t / j.n_colchunk) % j.n_rowblk);
                 tc::tma_load_2d(base + stage * stage_bytes, &tm, bar + 8 * stage, cc * j.box_cols, rb * j.box_rows);
+            } else if (j.mode == 2) {
+                const unsigned long long nblk = (unsigned long long)j.n_rowblk;
+                dwt::bulk_load_1d(base + stage * stage_bytes, (const char *)j.raw + (size_t)((unsigned long long)t % nblk) * j.box_bytes, j.box_bytes, bar + 8 * stage);
             } else {
                 const int ch = (int)(t % j.nch), b = (int)((t / j.nch) % j.B);
                 dwt::tma_load_4d(base + stage * stage_bytes, &tm, bar + 8 * stage, ch * j.chunk_elems, j.x0, j.y0, b);
@@ -208,6 +212,11 @@ int main(int argc, char **argv) {
         run("2-D 128ch x 128 rows  SWIZZLE_NONE (256-byte rows)", map2d(p, 768, (uint64_t)B * H * W, LD * 2, 128, 128, CU_TENSOR_MAP_SWIZZLE_NONE), m, 128, 1.0);
         Job q = j; q.box_cols = 256; q.box_bytes = 128 * 512; q.n_colchunk = 3; q.boxes_per_cta = j.boxes_per_cta / 4;
         run("2-D 256ch x 128 rows  SWIZZLE_NONE (512-byte rows)", map2d(p, 768, (uint64_t)B * H * W, LD * 2, 256, 128, CU_TENSOR_MAP_SWIZZLE_NONE), q, 128, 1.0);
+    }
+    for (uint32_t bytes : {16384u, 32768u, 49152u}) {   // the same bytes as contiguous blocks: one cp.async.bulk per block, no tensor map
+        Job j{}; j.mode = 2; j.box_bytes = bytes; j.raw = p; j.n_rowblk = (int)(n * 2 / bytes); j.boxes_per_cta = (int)(n * 2 / bytes / 148) * reps;
+        char nm[96]; snprintf(nm, sizeof nm, "1-D bulk copy of %u-byte contiguous blocks", bytes);
+        run(nm, map2d(p, 768, (uint64_t)B * H * W, LD * 2, 64, 128, CU_TENSOR_MAP_SWIZZLE_128B), j, (int)(bytes / 128), 1.0);
     }
     {   // depthwise halo box on the 19x19 map: 64ch x 22 x 21, origin (-1,-1)
         Job j{}; j.mode = 1; j.boxes_per_cta = per; j.nch = 12; j.B = B; j.chunk_elems = 64; j.x0 = -1; j.y0 = -1; j.box_bytes = 22 * 21 * 128;
