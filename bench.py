@@ -7,8 +7,11 @@
 
 A step = one pass of the hot path over one batch of `--batch` synthetic 299x299x3 uint8 images per GPU.
   value : images/s with the source pixels already resident in HBM (CUDA events, max over ranks)
-  e2e   : images/s through the host-facing C-ABI call (kdl_predict_u8_host): pinned host pixels -> H2D -> kernels
-          -> D2H logits, every step
+  e2e   : images/s through the host-facing C-ABI call (kdl_submit_u8_host / kdl_wait): pinned host pixels -> H2D ->
+          kernels -> D2H logits, every step
+  configs : the other BASELINE.json configurations measured in the same process (rank 0): batch 64 @299, batch 256 @150
+          with its own dominant-kernel roofline, mixed-size end-to-end latency at batch 1/8/32, batch-1 latency, and the
+          STRONG-scaling leg of configs[3] (1024 images split 1024/N per rank, pinned host pixels -> logits gathered on rank 0)
 Prints ONE JSON line (rank 0).
 """
 import argparse
@@ -95,6 +98,21 @@ class ClockSampler:
                 "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def workload_config(args):
+    """The `config` object of the JSON line -- identical for the kdl arm and the --impl reference arm (the reference arm runs a
+    bounded sample of this workload and says so in cpu_baseline.sample)."""
+    B, S = args.batch, args.size
+    return {"workload": f"Xception-{S} fused uint8->logits, bf16, batch {B}/GPU", "batch_per_gpu": B,
+            "input": f"{S}x{S}x3 uint8 U{{0..255}}, random-init calibrated weights seed 1",
+            "parallelism": f"replicas x{args.gpus} (no collective)",
+            "l2": f"2 input sets rotated; per-step activation working set (~{B * 155.1 / 1e3:.1f} GB at bs {B}) >> 126 MB L2"}
+
+
+def percentiles(ts):
+    ts = sorted(ts)
+    return {"p50_ms": ts[len(ts) // 2], "p99_ms": ts[min(len(ts) - 1, int(len(ts) * 0.99))], "calls": len(ts)}
+
+
 def cpu_reference_rate(n_images, size, steps=1, warmup=0, seed=1234):
     """The path's CPU implementation: Pillow NEAREST resize + numpy fp32 scaling (the reference's real
     preprocessing code) + the torch-CPU fp32 restatement of the Keras/TF forward, on all host threads.
@@ -129,6 +147,7 @@ def main():
     ap.add_argument("--size", type=int, default=299)
     ap.add_argument("--cpu-sample", type=int, default=48, help="images in the bounded CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the `configs` block (other BASELINE.json configurations)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "kdl" else args.warmup
     # The contract is ONE JSON line on stdout.  Libraries print there too (NCCL's version banner comes from C code), so file
@@ -140,22 +159,24 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    workload = f"Xception-{args.size} fused uint8->logits, bf16, batch {args.batch}/GPU"
+    config = workload_config(args)
 
     # ------------------------------------------------------------------ reference arm (CPU)
     if args.impl == "reference":
         if rank != 0:
             return
-        sample = 16
-        rate, sec, threads = cpu_reference_rate(sample, args.size, steps=args.steps, warmup=min(args.warmup, 2))
+        sample = 16     # bounded sample of the workload per step: img/s of the CPU path does not depend on the batch size
+        rate, sec, threads = cpu_reference_rate(sample, args.size, steps=args.steps, warmup=args.warmup)
         line = {
             "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": min(args.warmup, 2), "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload, "note": "reference CPU path: Pillow NEAREST resize + numpy x/127.5-1 (real reference "
-                       "code) + torch-CPU fp32 restatement of the Keras/TF-2.3.0 Xception forward (TF not installable offline)"},
+            "config": config,
+            "note": "reference CPU path: Pillow NEAREST resize + numpy x/127.5-1 (real reference code) + torch-CPU fp32 "
+                    "restatement of the Keras/TF-2.3.0 Xception forward (TF not installable offline)",
             "cpu_baseline": {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
-                             "sample": f"{sample} images of {args.size}x{args.size}x3 uint8 per step"},
+                             "sample": f"each step = a bounded sample of the workload: {sample} images of {args.size}x{args.size}x3 "
+                                       f"uint8 (not the full batch of {args.batch}); ms_per_step is per sample"},
             "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
         }
@@ -172,7 +193,6 @@ def main():
     torch.cuda.set_device(local_rank)
     dist = None
     if world > 1:
-        os.environ["NCCL_DEBUG"] = "WARN"   # keep NCCL's version banner off stdout: the contract is ONE JSON line
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
@@ -207,6 +227,7 @@ def main():
     clocks = ClockSampler(local_rank)
     if rank == 0:
         clocks.start()
+        time.sleep(0.15)                     # let the sampler deliver its first lines before the short timed region
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
     for i in range(K):
@@ -258,15 +279,67 @@ def main():
         for _ in range(20):
             model.predict_packed_host(one, h1)
         lat = []
-        for _ in range(300):
+        for _ in range(1000):
             t0 = time.perf_counter()
             model.predict_packed_host(one, h1)
             lat.append((time.perf_counter() - t0) * 1e3)
-        lat.sort()
-        latency = {"p50_ms": lat[len(lat) // 2], "p99_ms": lat[int(len(lat) * 0.99)], "calls": len(lat),
-                   "launches_per_call": model.last_launch_count,
-                   "api": "kdl_predict_u8_host, batch 1, host pixels -> host logits (CUDA-graph replay of the forward)"}
+        latency = dict(percentiles(lat), launches_per_call=model.last_launch_count,
+                       api="kdl_predict_u8_host, batch 1, host pixels -> host logits (CUDA-graph replay of the forward)")
     barrier()
+
+    # ---- configs[3], STRONG scaling: 1024 images in total, 1024/N per rank, timed from "pixels in pinned host memory" to
+    # "all logits gathered in one host buffer on rank 0" (replicas.gather_logits inside the timed region).  Rank 0 also runs the
+    # whole 1024 alone in the same process, so efficiency_vs_n1 compares like with like on this box.
+    strong = None
+    if not args.no_configs:
+        from kdl_b200 import replicas
+        TOTAL = 1024
+        lo, hi = replicas.shard_range(TOTAL, rank, world)
+
+        def make_chunks(lo, hi):
+            ch = []
+            for c0 in range(lo, hi, B):
+                n = min(B, hi - c0)
+                ch.append((engine.PackedImages(synth_images(n, S, 5000 + c0), pinned=True),
+                           torch.empty((n, 10), dtype=torch.float32).pin_memory()))
+            return ch
+
+        def run_chunks(ch):
+            for pk, o in ch:
+                model.submit_packed_host(pk, o)      # at most two in flight; a third submit retires the oldest itself
+            model.wait(); model.wait()
+            return np.concatenate([o.numpy()[:pk.B] for pk, o in ch]) if ch else np.empty((0, 10), np.float32)
+
+        def timed(fn, reps):
+            fn()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                r = fn()
+            barrier()
+            return max_over_ranks(time.perf_counter() - t0) / reps, r
+
+        mine = make_chunks(lo, hi)
+        reps = max(3, min(K, 10))
+        sec, gathered = timed(lambda: replicas.gather_logits(run_chunks(mine)), reps)
+        strong = {"images": TOTAL, "per_rank": hi - lo, "value": TOTAL / sec, "unit": UNIT, "ms_per_pass": sec * 1e3, "passes": reps,
+                  "what": "pinned host pixels -> H2D -> kernels -> D2H -> logits of all ranks gathered on rank 0 (host)"}
+        if rank == 0:
+            assert gathered is not None and gathered.shape == (TOTAL, 10)
+        if world > 1:
+            if rank == 0:
+                alone = make_chunks(0, TOTAL)
+                t0 = time.perf_counter()
+                run_chunks(alone)                                   # warm
+                t0 = time.perf_counter()
+                for _ in range(reps):
+                    run_chunks(alone)
+                n1 = TOTAL * reps / (time.perf_counter() - t0)
+                strong["n1_same_process_value"] = n1
+                strong["efficiency_vs_n1"] = strong["value"] / (world * n1)
+            barrier()
+        else:
+            strong["efficiency_vs_n1"] = 1.0
 
     # ---- per-kernel roofline: CUDA events around every launch, same steps, on the launching stream
     peaks = load_peaks()
@@ -301,21 +374,83 @@ def main():
                  "peak_source": peaks["_source"] + (" sustained bf16" if dom["bound"] == "tensor" else " copy bandwidth"),
                  "timing": f"cuda events around each launch over {K} steps (separate pass right after the timed region)"})
 
+    # ---- the other BASELINE.json configurations, same process (rank 0)
+    configs = None
+    if rank == 0 and not args.no_configs:
+        configs = {}
+
+        def device_rate(mdl, b, size, steps=K):
+            pk = [engine.PackedImages(synth_images(b, size, 300 + i), pinned=True) for i in range(2)]
+            dv = [q.host.cuda() for q in pk]
+            o = torch.empty((b, 10), dtype=torch.float32, device="cuda")
+            for i in range(3):
+                mdl.predict_packed_device(dv[i % 2], pk[i % 2], o)
+            torch.cuda.synchronize()
+            a, z = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream)
+            for i in range(steps):
+                mdl.predict_packed_device(dv[i % 2], pk[i % 2], o)
+            z.record(stream)
+            torch.cuda.synchronize()
+            return b * steps / (a.elapsed_time(z) * 1e-3), a.elapsed_time(z) / steps, pk, dv, o
+
+        if B >= 64:
+            r64, ms64, *_ = device_rate(model, 64, S)
+            configs["b64"] = {"workload": f"Xception-{S} bf16 batch 64, device-resident", "value": r64, "unit": UNIT, "ms_per_step": ms64}
+        # configs[2]: the small-input variant at batch 256 with its own dominant-kernel roofline
+        m150 = engine.Model(Wt, device=local_rank, max_batch=B, input_size=150, precision="bf16")
+        r150, ms150, pk150, dv150, o150 = device_rate(m150, B, 150)
+        m150.profile_begin()
+        for i in range(K):
+            m150.predict_packed_device(dv150[i % 2], pk150[i % 2], o150)
+        rows150 = m150.profile_end()
+        m150.close()
+        d150 = max(rows150, key=lambda r: r["ms"])
+        tb = "tensor-bound" in d150["kernel"]
+        ach = (d150["flops"] / 1e12 if tb else d150["bytes"] / 1e9) / (d150["ms"] * 1e-3)
+        pk_ = peaks["bf16_tflops_sustained"] if tb else peaks["hbm_gbs"]
+        configs["b256_150"] = {"workload": f"Xception-150 bf16 batch {B}, device-resident", "value": r150, "unit": UNIT, "ms_per_step": ms150,
+                               "roofline": {"kernel": d150["kernel"], "bound": "tensor" if tb else "hbm", "achieved": ach, "peak": pk_,
+                                            "unit": "TFLOP/s" if tb else "GB/s", "frac": ach / pk_, "launches_per_step": d150["launches"] // K,
+                                            "ms_per_step": d150["ms"] / K, "share": d150["ms"] / (sum(r["ms"] for r in rows150) or 1.0)}}
+        # configs[4]: mixed-size sources (64..2048)^2, host pixels -> host logits through kdl_predict_u8_host, >= 500 calls each
+        rng = np.random.default_rng(2)
+        mixed = {}
+        for b in (1, 8, 32):
+            if b > B:
+                continue
+            sets = [engine.PackedImages([rng.integers(0, 256, (int(rng.integers(64, 2049)), int(rng.integers(64, 2049)), 3), dtype=np.uint8)
+                                         for _ in range(b)], pinned=True) for _ in range(4)]
+            h = np.empty((b, 10), np.float32)
+            for c in sets * 2:
+                model.predict_packed_host(c, h)
+            ts = []
+            for i in range(500):
+                t0 = time.perf_counter()
+                model.predict_packed_host(sets[i % len(sets)], h)
+                ts.append((time.perf_counter() - t0) * 1e3)
+            mixed[f"b{b}"] = dict(percentiles(ts), mean_src_mb=float(np.mean([c.total_bytes for c in sets]) / 1e6))
+            del sets
+        configs["mixed_size_e2e_latency"] = dict(mixed, api="kdl_predict_u8_host: pinned host pixels of mixed sizes (64..2048)^2 -> "
+                                                 "H2D -> fused resize+scale -> Xception -> D2H logits")
+        configs["latency_b1"] = latency
+    if strong is not None and rank == 0:
+        configs = configs if configs is not None else {}
+        configs["strong_b1024"] = strong
+
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
         "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
         "data": "synthetic",
-        "config": {"workload": workload, "batch_per_gpu": B, "input": f"{S}x{S}x3 uint8 U{{0..255}}, random-init calibrated weights seed 1",
-                   "parallelism": f"replicas x{world} (no collective)",
-                   "l2": f"{NSETS} input sets rotated; per-step activation working set (~{B * 155.1 / 1e3:.1f} GB at bs {B}) >> 126 MB L2"},
+        "config": config,
         "e2e": e2e, "gpu_launches": launches_per_step * K, "clocks": clk, "roofline": roof, "kernels": kernels,
-        "latency_b1": latency,
+        "latency_b1": latency, "configs": configs,
     }
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        rate, sec, threads = cpu_reference_rate(args.cpu_sample, S, steps=1, warmup=0)
+        rate, sec, threads = cpu_reference_rate(args.cpu_sample, S, steps=1, warmup=1)
         line["cpu_baseline"] = {"value": rate, "unit": UNIT, "cores": threads, "kind": "port",
-                                "sample": f"{args.cpu_sample} images of {S}x{S}x3 uint8, one pass ({sec:.1f} s): Pillow resize+scale "
+                                "sample": f"{args.cpu_sample} images of {S}x{S}x3 uint8, one timed pass after one warm-up pass ({sec:.1f} s): Pillow resize+scale "
                                           "(reference code) + torch-CPU fp32 restatement of the TF forward",
                                 "host_cpus": os.cpu_count()}
     model.close()

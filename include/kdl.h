@@ -51,6 +51,28 @@ typedef struct KdlConfig {
     int32_t use_graphs;   /* !=0: replay the forward pass as a CUDA graph from the 3rd call with the same (batch, input buffer) on */
 } KdlConfig;
 
+/* Kernel-selection switches of one model (no reference counterpart: TF-Serving has no such knobs; these exist so that A/B
+ * measurements and the bit-identity tests of tests/test_gpu_variants.py do not depend on hidden environment variables).
+ * kdl_create installs the defaults; kdl_set_tuning takes effect from the next forward pass and drops the cached CUDA graphs.
+ * All variants compute the same arithmetic in the same order: results are bit-identical whatever is selected. */
+typedef struct KdlTuning {
+    int32_t pdl_max_batch;       /* programmatic dependent launch for forwards of at most this many images (default 64; 0 = never) */
+    int32_t serpentine;          /* !=0 (default): kernels walk their tiles in alternating directions so a consumer starts on the
+                                    rows its producer wrote last (activations exceed the 126 MB L2 at large batch) */
+    int32_t conv2_shifted_taps;  /* !=0: block1_conv2 as 9 shifted TMA boxes per tile instead of the staged halo (default 0) */
+    int32_t fused_sepconv;       /* !=0 (default): blocks 2-3 run the fused depthwise+pointwise kernel */
+    int32_t dw_direct_store;     /* !=0: depthwise kernels store straight from registers instead of smem + TMA store (default 0) */
+    int32_t fused_midflow;       /* !=0 (default): 728 -> 728 layers at 19 x 19 (middle flow, block13_sepconv1) run the fused
+                                    depthwise+pointwise kernel with flat-pixel tiles (sepconv_mid.cuh) */
+    int32_t reserved[6];         /* must be 0 */
+} KdlTuning;
+int kdl_get_tuning(const KdlModel *m, KdlTuning *out);
+int kdl_set_tuning(KdlModel *m, const KdlTuning *t);
+
+/* CUDA-graph cache counters (cfg.use_graphs): entries cached, captures, replays and LRU evictions so far.  The cache holds
+ * max_batch + 8 keys (16..264), so a dynamic batcher cycling through every batch size keeps replaying. */
+int kdl_graph_stats(const KdlModel *m, int32_t *cached, int32_t *captures, int32_t *replays, int32_t *evictions);
+
 /* Model lifecycle.  Replaces TF-Serving loading /models/clothing-model/1 at container start
  * (tf-serving.dockerfile:4-5). */
 int kdl_create(const KdlConfig *cfg, KdlModel **out);
@@ -130,8 +152,7 @@ int kdl_last_launch_count(const KdlModel *m);
 
 /* Stand-alone pointwise GEMM entry (kernel-level parity and roofline measurement):
  * out[M,N] = act( A[M,K] * W[K,N] + bias[N] ) (+ residual[M,N]); bf16 device buffers, W given K-major
- * as Wt[N,K]; residual may be NULL.  `relu` bit 0 = apply ReLU; bit 1 = force the single-CTA 128x256 tcgen05 kernel (default: the
- * CTA-pair cta_group::2 kernel when M >= 256); bit 2 = the 256x256-per-CTA kernel. */
+ * as Wt[N,K]; residual may be NULL.  `relu` bit 0 = apply ReLU (other bits ignored).  Runs the same k_gemm_tc the model uses. */
 int kdl_gemm_bf16(const void *d_A, const void *d_Wt, const float *d_bias, const void *d_residual,
                   void *d_out, int32_t M, int32_t N, int32_t K, int32_t relu, void *stream);
 
@@ -148,6 +169,8 @@ int kdl_gemm_bf16(const void *d_A, const void *d_Wt, const float *d_bias, const 
  *   - All calls on a device share the array and it keeps the previous call's contents.  Nothing needs clearing (each call
  *     rewrites every entry it reads), but two calls whose kernels overlap on the GPU (different streams, or threads racing on
  *     one stream) corrupt each other: serialise them on one stream or with events.
+ *   - d_out must be 16-byte aligned (the kernel writes float4 vectors; kdl_preprocess_u8 accepts any alignment, this entry
+ *     refuses a misaligned pointer with KDL_EINVAL rather than fault on the device).
  *   - offset/h/w/pitch are HOST arrays of length B, as for kdl_preprocess_u8.  Errors: text is copied into err (may be NULL). */
 #define KDL_STATIC_MAX_BATCH 32
 #define KDL_STATIC_MAX_SIZE 512

@@ -17,6 +17,7 @@ SYMBOLS = [
     "kdl_preprocess_u8", "kdl_forward", "kdl_predict_u8", "kdl_predict_u8_host", "kdl_forward_host",
     "kdl_num_taps", "kdl_tap_name", "kdl_layer_output", "kdl_last_launch_count", "kdl_gemm_bf16",
     "kdl_version", "kdl_profile_begin", "kdl_profile_end", "kdl_preprocess_u8_static", "kdl_submit_u8_host", "kdl_wait",
+    "kdl_get_tuning", "kdl_set_tuning", "kdl_graph_stats",
 ]
 STATIC_MAX_BATCH, STATIC_MAX_SIZE = 32, 512
 
@@ -24,6 +25,11 @@ STATIC_MAX_BATCH, STATIC_MAX_SIZE = 32, 512
 class KdlConfig(ctypes.Structure):
     _fields_ = [("device", c_int32), ("max_batch", c_int32), ("input_size", c_int32), ("head_inner", c_int32),
                 ("precision", c_int32), ("gemm_impl", c_int32), ("keep_taps", c_int32), ("use_graphs", c_int32)]
+
+
+class KdlTuning(ctypes.Structure):
+    _fields_ = [("pdl_max_batch", c_int32), ("serpentine", c_int32), ("conv2_shifted_taps", c_int32), ("fused_sepconv", c_int32),
+                ("dw_direct_store", c_int32), ("fused_midflow", c_int32), ("reserved", c_int32 * 6)]
 
 
 class KdlProfileRow(ctypes.Structure):
@@ -73,6 +79,9 @@ def load():
     lib.kdl_gemm_bf16.argtypes = [P, P, P, P, P, c_int32, c_int32, c_int32, c_int32, P]
     lib.kdl_version.restype = c_char_p
     lib.kdl_preprocess_u8_static.argtypes = [P, P, P, P, P, c_int32, c_int32, P, P, c_char_p, c_size_t]
+    lib.kdl_get_tuning.argtypes = [P, POINTER(KdlTuning)]
+    lib.kdl_set_tuning.argtypes = [P, POINTER(KdlTuning)]
+    lib.kdl_graph_stats.argtypes = [P, POINTER(c_int32), POINTER(c_int32), POINTER(c_int32), POINTER(c_int32)]
     lib.kdl_profile_begin.argtypes = [P]
     lib.kdl_profile_end.argtypes = [P, POINTER(KdlProfileRow), c_int32, POINTER(c_int32)]
     for s in SYMBOLS:

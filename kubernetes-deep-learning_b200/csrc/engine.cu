@@ -15,12 +15,11 @@
 
 #include "../../include/kdl.h"
 #include "gemm_tc.cuh"
-#include "gemm_tc2.cuh"
-#include "gemm_tc_m2.cuh"
 #include "conv_tc.cuh"
 #include "dw_tma.cuh"
 #include "pool_tma.cuh"
 #include "sepconv_tc.cuh"
+#include "sepconv_mid.cuh"
 #include "kernels.cuh"
 
 using namespace kdl;
@@ -84,9 +83,9 @@ struct GemmW {
     void *Wkn = nullptr;   // storage T, [K][N]  (CUDA-core GEMM)
     bf16 *Wnk = nullptr;   // bf16, [N][K]       (tcgen05 GEMM, K-major B operand)
     float *bias = nullptr; // folded BN shift
-    CUtensorMap tmB;       // TMA descriptor of Wnk (box 64 x 256: single-CTA kernel)
-    CUtensorMap tmB2;      // TMA descriptor of Wnk (box 64 x 128: each CTA of a pair loads half of the N tile)
+    CUtensorMap tmB;       // TMA descriptor of Wnk (box 64 x 256)
     CUtensorMap tmB64;     // TMA descriptor of Wnk (box 64 x 64: small-M tiling)
+    CUtensorMap tmB192;    // TMA descriptor of Wnk (box 64 x 192: the fused middle-flow kernel's two N sub-tiles)
 };
 
 struct Tap {
@@ -101,13 +100,7 @@ struct KdlModel {
     KdlConfig cfg;
     char err[512];
     bool weights_loaded = false;
-    bool no_fused_sepconv = false;   // KDL_NO_FUSED_SEPCONV=1: separate depthwise + pointwise kernels everywhere (A/B)
-    int microbatch_mb = 0;           // KDL_MICROBATCH_MB: size (MiB) of the L2-resident depthwise->pointwise hand-off, 0 = off
-    bool serpentine = true;          // KDL_SERPENTINE=0 turns the alternating tile order off (A/B measurements)
-    int pdl_max_batch = 64;          // programmatic dependent launch for forwards of at most this many images (launch-latency-bound
-                                     // regime: -9 % at batch 1, -5 % at 8, -1 % at 64; at 256 +0.4 % device but -1.5 % end to end); KDL_PDL=0 never, KDL_PDL=1 always
-    bool conv_shifted_taps = false;  // KDL_CONV2_TAPS=1: 9 shifted TMA boxes per tile instead of the staged halo (A/B)
-    int gemm_variant = 1;     // KDL_GEMM_VARIANT: tensor-bound layers use 1 = 128x256 single CTA, 2 = CTA pair (cta_group::2), 3 = 256x256 per CTA
+    KdlTuning tune;                  // kernel-selection switches (kdl_set_tuning; defaults in default_tuning())
     int launches = 0;
     int last_B = 0;
     int sp[7];  // spatial chain S,H1..H6
@@ -151,8 +144,10 @@ struct KdlModel {
     tc::TmaEncoder tma;
 
     // CUDA graphs of the forward pass, keyed by (batch, input pointer)
-    struct GraphEntry { int B; const float *in_f32; const uint8_t *in_u8; cudaGraphExec_t exec; int launches; };
+    struct GraphEntry { int B; const float *in_f32; const uint8_t *in_u8; cudaGraphExec_t exec; int launches; uint64_t last_use; };
     std::vector<GraphEntry> graphs;
+    uint64_t graph_clock = 0;
+    int graph_replays = 0, graph_captures = 0, graph_evictions = 0;   // kdl_graph_stats
 
     // per-launch CUDA-event profiling (kdl_profile_begin / kdl_profile_end)
     bool profiling = false;
@@ -164,10 +159,10 @@ struct KdlModel {
     int cls_launches[16];
 };
 
-enum ProfClass { PC_RESIZE = 0, PC_CONV1, PC_CONV2, PC_DW, PC_PW_TC_HBM, PC_PW_TC_TENSOR, PC_GEMM_SIMPLE, PC_SUBSAMPLE, PC_POOL, PC_HEAD, PC_SEPFUSED, PC_COUNT };
+enum ProfClass { PC_RESIZE = 0, PC_CONV1, PC_CONV2, PC_DW, PC_PW_TC_HBM, PC_PW_TC_TENSOR, PC_GEMM_SIMPLE, PC_SUBSAMPLE, PC_POOL, PC_HEAD, PC_SEPFUSED, PC_SEPMID, PC_COUNT };
 static const char *PROF_NAMES[PC_COUNT] = {"k_resize", "k_conv1", "conv2_implicit_gemm", "k_dw3x3", "k_gemm_tc[K<=256,hbm-bound]",
                                            "k_gemm_tc[K>=728,tensor-bound]", "k_gemm_simple", "k_subsample2", "k_maxpool_add", "k_gap_partial+k_head_finish",
-                                           "k_sepconv_tc[fused dw+pw,hbm-bound]"};
+                                           "k_sepconv_tc[fused dw+pw,hbm-bound]", "k_sepconv_mid[fused dw+pw,tensor-bound]"};
 
 static cudaEvent_t prof_event(KdlModel *m) {
     if (m->ev_used == m->ev_pool.size()) {
@@ -192,6 +187,19 @@ static void prof_close(KdlModel *m, cudaStream_t st) {
 }
 
 template <typename T> struct Runner;
+
+// Kernel-selection defaults (KdlTuning in kdl.h).  Programmatic dependent launch pays in the launch-latency-bound regime
+// (-9 % at batch 1, -5 % at 8, -1 % at 64; at 256 +0.4 % on the device but -1.5 % end to end), hence the batch threshold.
+static KdlTuning default_tuning() {
+    KdlTuning t;
+    memset(&t, 0, sizeof t);
+    t.pdl_max_batch = 64;
+    t.serpentine = 1;
+    t.conv2_shifted_taps = 0;
+    t.fused_sepconv = 1;
+    t.fused_midflow = 1;
+    return t;
+}
 
 static int dev_alloc(KdlModel *m, void **p, size_t bytes) {
     char *err = m->err;
@@ -230,7 +238,7 @@ template <typename T> struct Runner {
     // order finds the start already evicted and thrashes (ncu: the pointwise GEMM re-read ALL of its input from DRAM).  A kernel
     // that can walk its tiles backwards therefore runs opposite to the kernel before it: it starts on the freshest data.
     int prev_rev = 0;
-    int flip() { prev_rev = m->serpentine ? 1 - prev_rev : 0; return prev_rev; }
+    int flip() { prev_rev = m->tune.serpentine ? 1 - prev_rev : 0; return prev_rev; }
     void no_flip() { prev_rev = 0; }   // a kernel without a reverse mode ran forwards
 
     int alloc_tap(const char *name, int H, int C, int relu_applied, bool is_float, int *idx) {
@@ -296,16 +304,7 @@ template <typename T> struct Runner {
         const double bytes = ((double)M * g.K + (double)M * g.N * (resid ? 2 : 1) + (double)g.K * g.N) * sizeof(T) + 4.0 * g.N;
         if (use_tc() && rm.mode == 0 && tc::shape_supported(M, g.N, g.K)) {
             prof_open(m, st, g.K >= 512 ? PC_PW_TC_TENSOR : PC_PW_TC_HBM, flops, bytes, "gemm M=%d N=%d K=%d", M, g.N, g.K);
-            int rc;
-            if ((m->gemm_variant == 2 || m->gemm_variant == 3) && M >= 2048 && g.K >= 512) no_flip();
-            if (m->gemm_variant == 3 && M >= 2048 && g.K >= 512)  // 256x256 tile per CTA (two M tiles share each weight block)
-                rc = tcm2::launch(m->tma, (const bf16 *)A, &g.tmB, g.bias, (const bf16 *)resid, (bf16 *)out, M, g.N, g.K, relu, st, m->err,
-                                  ld(g.K), ld(g.N));
-            else if (m->gemm_variant == 2 && M >= 2048 && g.K >= 512)  // CTA pair (cta_group::2)
-                rc = tc2::launch_gemm2(m->tma, (const bf16 *)A, &g.tmB2, g.bias, (const bf16 *)resid, (bf16 *)out, M, g.N, g.K, relu,
-                                       st, m->err, ld(g.K), ld(g.N));
-            else
-                rc = tc::launch_gemm(m->tma, (const bf16 *)A, &g.tmB, g.bias, (const bf16 *)resid, (bf16 *)out,
+            int rc = tc::launch_gemm(m->tma, (const bf16 *)A, &g.tmB, g.bias, (const bf16 *)resid, (bf16 *)out,
                                      M, g.N, g.K, relu, st, m->err, ld(g.K), ld(g.N), &g.tmB64, flip());
             prof_close(m, st);
             if (rc != KDL_OK) return rc;
@@ -320,31 +319,15 @@ template <typename T> struct Runner {
         return KDL_OK;
     }
 
-    // depthwise -> pointwise of one SeparableConv2D.  For the big early layers (K <= 256, HBM-bound) the batch is walked in
-    // micro-batches that all reuse the SAME small region of the T buffer: the depthwise output of micro-batch i is consumed by
-    // its GEMM while still in L2 and overwritten by micro-batch i+1 before it is ever written back, so the intermediate tensor
-    // costs (almost) no HBM traffic.
+    // depthwise -> pointwise of one SeparableConv2D as two kernels (T holds the depthwise output)
     int sepconv(const T *in, int si, T *out, int H, int relu_in, int relu_out) {
         const GemmW &g = m->pw[si];
         const RowMap dense{0, 0, 0, 0, 0, 0};
-        T *Tb = (T *)m->T;
-        int mb = B;
-        if (use_tc() && m->microbatch_mb > 0 && g.K <= 256) {
-            size_t per_img = (size_t)H * H * ld(g.K) * sizeof(T);
-            mb = (int)((size_t)m->microbatch_mb * (1u << 20) / per_img);
-            if (mb < 1) mb = 1;
-            if (mb > B) mb = B;
-        }
-        for (int b0 = 0; b0 < B; b0 += mb) {
-            const int nb = (B - b0) < mb ? (B - b0) : mb;
-            const size_t ioff = (size_t)b0 * H * H * ld(g.K), ooff = (size_t)b0 * H * H * ld(g.N);
-            RUN(dwconv(in + ioff, m->dw[si], m->dwpad[si], Tb, H, g.K, relu_in, nb));
-            RUN(gemm(Tb, g, nullptr, out + ooff, nb * H * H, relu_out, dense));
-        }
-        return KDL_OK;
+        RUN(dwconv(in, m->dw[si], m->dwpad[si], (T *)m->T, H, g.K, relu_in));
+        return gemm((T *)m->T, g, nullptr, out, B * H * H, relu_out, dense);
     }
 
-    bool can_fuse(int si) const { return use_tc() && !m->no_fused_sepconv && sepc::supported(m->pw[si].K, m->pw[si].N); }
+    bool can_fuse(int si) const { return use_tc() && m->tune.fused_sepconv && sepc::supported(m->pw[si].K, m->pw[si].N); }
     // fused depthwise+pointwise (sepconv_tc.cuh); in and out must be different buffers (tiles read a halo)
     int sepconv_fused(const T *in, int si, T *out, int H, int relu_in, int relu_out) {
         const GemmW &g = m->pw[si];
@@ -354,6 +337,24 @@ template <typename T> struct Runner {
         no_flip();
         int rc = sepc::launch(m->tma, (const bf16 *)in, m->dwpad[si], &g.tmB, g.bias, (bf16 *)out, B, H, H, g.K, g.N, ld(g.K), ld(g.N),
                               relu_in, relu_out, st, m->err);
+        prof_close(m, st);
+        if (rc != KDL_OK) return rc;
+        m->launches++;
+        return KDL_OK;
+    }
+
+    // middle-flow shape (K, N <= 768 at W <= 20): fused depthwise + pointwise with flat-pixel tiles (sepconv_mid.cuh); resid may alias out
+    bool can_fuse_mid(int si, int H) const {
+        return use_tc() && m->tune.fused_midflow && sepm::supported(H, H, m->pw[si].K, m->pw[si].N);
+    }
+    int sepconv_mid(const T *in, int si, const T *resid, T *out, int H, int relu_in, int relu_out) {
+        const GemmW &g = m->pw[si];
+        const double px = (double)B * H * H;
+        prof_open(m, st, PC_SEPMID, 2.0 * px * (9.0 * g.K + (double)g.K * g.N),
+                  (px * g.K + px * g.N * (resid ? 2 : 1) + (double)g.K * g.N) * 2.0 + 36.0 * g.K, "sepmid H=%d K=%d N=%d", H, g.K, g.N);
+        no_flip();
+        int rc = sepm::launch(m->tma, (const bf16 *)in, m->dwpad[si], &g.tmB192, g.bias, (const bf16 *)resid, (bf16 *)out, B, H, H, g.K, g.N,
+                              ld(g.K), ld(g.N), relu_in, relu_out, st, m->err);
         prof_close(m, st);
         if (rc != KDL_OK) return rc;
         m->launches++;
@@ -421,7 +422,7 @@ template <typename T> struct Runner {
             if (use_tc()) {
                 prof_open(m, st, PC_CONV2, 2.0 * B * sp[2] * sp[2] * 288.0 * 64.0,
                           ((double)B * sp[1] * sp[1] * 32 + (double)B * sp[2] * sp[2] * 64 + 288.0 * 64) * 2.0);
-                int rc = (convtc::geometry_supported(sp[1]) && !m->conv_shifted_taps)
+                int rc = (convtc::geometry_supported(sp[1]) && !m->tune.conv2_shifted_taps)
                              ? convtc::launch(m->tma, (const bf16 *)U, &m->conv2.tmB, m->conv2.bias, (bf16 *)X, (bf16 *)m->S, B, sp[1], sp[1], 1, st, m->err)
                              : tc::launch_conv3x3(m->tma, (const bf16 *)U, &m->conv2.tmB, m->conv2.bias, (bf16 *)X, B, sp[1], sp[1], 1, st, m->err);
                 prof_close(m, st);
@@ -435,7 +436,7 @@ template <typename T> struct Runner {
         // ---- entry/exit blocks with projection + pool: 2,3,4 then middle, then 13 ----
         int si = 0;  // sepconv index
         // S already holds the even pixels of X when the producer of X wrote them (conv2's epilogue, the pool kernels of blocks 2-3)
-        bool have_sub = use_tc() && convtc::geometry_supported(sp[1]) && !m->conv_shifted_taps;
+        bool have_sub = use_tc() && convtc::geometry_supported(sp[1]) && !m->tune.conv2_shifted_taps;
         auto entry_block = [&](int blk, int ri, int H, int Ho) -> int {
             const GemmW &rg = m->res[ri];
             RUN(projection(X, rg, R, H, Ho, have_sub));
@@ -443,6 +444,7 @@ template <typename T> struct Runner {
             RUN(tap(name, R, Ho, rg.N, 0));
             // sepconv1: ReLU on load except block2 (input is already post-ReLU there)
             if (can_fuse(si)) RUN(sepconv_fused(X, si, U, H, blk != 2, 1));
+            else if (can_fuse_mid(si, H)) RUN(sepconv_mid(X, si, nullptr, U, H, blk != 2, 1));   // block13_sepconv1 (728 -> 728 at 19 x 19)
             else RUN(sepconv(X, si, U, H, blk != 2, 1));  // next sepconv's ReLU folded into this GEMM's epilogue
             snprintf(name, sizeof name, "block%d_sepconv1_bn", blk);
             RUN(tap(name, U, H, m->pw[si].N, 1));
@@ -472,7 +474,23 @@ template <typename T> struct Runner {
         // ---- middle flow ----
         {
             const int H = sp[5], M = B * H * H;
+            const bool fuse_mid = can_fuse_mid(si, H);
             for (int blk = 5; blk <= 12; ++blk) {
+                if (fuse_mid) {   // X -> U -> T -> X (+X): the fused kernel reads a halo, so it never runs in place on its input
+                    RUN(sepconv_mid(X, si, nullptr, U, H, 1, 1));
+                    snprintf(name, sizeof name, "block%d_sepconv1_bn", blk);
+                    RUN(tap(name, U, H, 728, 1));
+                    ++si;
+                    RUN(sepconv_mid(U, si, nullptr, Tb, H, 0, 1));
+                    snprintf(name, sizeof name, "block%d_sepconv2_bn", blk);
+                    RUN(tap(name, Tb, H, 728, 1));
+                    ++si;
+                    RUN(sepconv_mid(Tb, si, X, X, H, 0, 0));      // + residual, in place on the skip tensor
+                    ++si;
+                    snprintf(name, sizeof name, "block%d_out", blk);
+                    RUN(tap(name, X, H, 728, 0));
+                    continue;
+                }
                 RUN(dwconv(X, m->dw[si], m->dwpad[si], Tb, H, 728, 1));
                 RUN(gemm(Tb, m->pw[si], nullptr, U, M, 1, dense));
                 snprintf(name, sizeof name, "block%d_sepconv1_bn", blk);
@@ -588,8 +606,8 @@ static int make_gemm(KdlModel *m, GemmW &g, const float *kern, int K, int N, con
     if (m->tma.ok()) {
         bool ok = conv3x3 ? m->tma.encode_2d(&g.tmB, g.Wnk, (uint64_t)K, (uint64_t)N, (uint64_t)Kp * 2, 32, 64, 64)
                           : m->tma.encode_2d(&g.tmB, g.Wnk, (uint64_t)K, (uint64_t)N, (uint64_t)Kp * 2, tc::BLOCK_K, tc::BLOCK_N, 128);
-        if (ok && !conv3x3) ok = m->tma.encode_2d(&g.tmB2, g.Wnk, (uint64_t)K, (uint64_t)N, (uint64_t)Kp * 2, tc2::BK2, 128, 128);
         if (ok && !conv3x3) ok = m->tma.encode_2d(&g.tmB64, g.Wnk, (uint64_t)K, (uint64_t)N, (uint64_t)Kp * 2, tc::BLOCK_K, 64, 128);
+        if (ok && !conv3x3) ok = m->tma.encode_2d(&g.tmB192, g.Wnk, (uint64_t)K, (uint64_t)N, (uint64_t)Kp * 2, tc::BLOCK_K, sepm::NSUB, 128);
         if (!ok) {
             set_err(m->err, "cuTensorMapEncodeTiled failed for weight [%d,%d]", N, K);
             return KDL_ECUDA;
@@ -763,14 +781,8 @@ extern "C" int kdl_create(const KdlConfig *cfg, KdlModel **out) {
         CKM(cudaEventCreateWithFlags(&m->slot_ev[i], cudaEventDisableTiming));
     }
     CKM(cudaStreamCreateWithFlags(&m->own_stream, cudaStreamNonBlocking));
-    { const char *e1 = getenv("KDL_GEMM_VARIANT"); m->gemm_variant = e1 ? atoi(e1) : 1; }
-    { const char *e1 = getenv("KDL_PDL"); if (e1 && e1[0] == '0') m->pdl_max_batch = 0; else if (e1 && e1[0] == '1') m->pdl_max_batch = 1 << 30; }
-    { const char *e1 = getenv("KDL_SERPENTINE"); if (e1 && e1[0] == '0') m->serpentine = false; }
-    { const char *e1 = getenv("KDL_PDL_MAX_BATCH"); if (e1 && atoi(e1) >= 0 && e1[0]) m->pdl_max_batch = atoi(e1); }
-    { const char *e1 = getenv("KDL_CONV2_TAPS"); m->conv_shifted_taps = e1 && e1[0] == '1'; }
-    { const char *e1 = getenv("KDL_MICROBATCH_MB"); m->microbatch_mb = e1 ? atoi(e1) : 0; }
-    { const char *e1 = getenv("KDL_NO_FUSED_SEPCONV"); m->no_fused_sepconv = e1 && e1[0] == '1'; }
-    if ((rc = tc::configure(m->err)) != KDL_OK || (rc = tc2::configure2(m->err)) != KDL_OK || (rc = tcm2::configure(m->err)) != KDL_OK || (rc = convtc::configure(m->err)) != KDL_OK || (rc = dwt::configure(m->err)) != KDL_OK || (rc = poolt::configure(m->err)) != KDL_OK || (rc = sepc::configure(m->err)) != KDL_OK) { set_err(g_err, "%s", m->err); kdl_destroy(m); return rc; }
+    m->tune = default_tuning();
+    if ((rc = tc::configure(m->err)) != KDL_OK || (rc = convtc::configure(m->err)) != KDL_OK || (rc = dwt::configure(m->err)) != KDL_OK || (rc = poolt::configure(m->err)) != KDL_OK || (rc = sepc::configure(m->err)) != KDL_OK || (rc = sepm::configure(m->err)) != KDL_OK) { set_err(g_err, "%s", m->err); kdl_destroy(m); return rc; }
 #undef CKM
     *out = m;
     return KDL_OK;
@@ -803,10 +815,27 @@ extern "C" int kdl_destroy(KdlModel *m) {
     return KDL_OK;
 }
 
+extern "C" int kdl_get_tuning(const KdlModel *m, KdlTuning *out) {
+    if (!m || !out) { set_err(g_err, "kdl_get_tuning: null argument"); return KDL_EINVAL; }
+    *out = m->tune;
+    return KDL_OK;
+}
+
+// Takes effect from the next forward pass; cached CUDA graphs were captured under the old selection and are dropped.
+static void drop_graphs(KdlModel *m);
+extern "C" int kdl_set_tuning(KdlModel *m, const KdlTuning *t) {
+    if (!m || !t) { set_err(g_err, "kdl_set_tuning: null argument"); return KDL_EINVAL; }
+    if (t->pdl_max_batch < 0) { set_err(m->err, "kdl_set_tuning: pdl_max_batch must be >= 0"); return KDL_EINVAL; }
+    cudaSetDevice(m->cfg.device);
+    drop_graphs(m);
+    m->tune = *t;
+    return KDL_OK;
+}
+
 extern "C" const char *kdl_last_error(const KdlModel *m) { return m ? m->err : g_err; }
 extern "C" int kdl_last_launch_count(const KdlModel *m) { return m ? m->launches : 0; }
 extern "C" const char *kdl_version(void) {
-    return "kdl 0.2 sm_100a: k_resize k_conv1 k_conv3x3_tc k_dw_tma k_sepconv_tc k_pool_tma k_gemm_tc(tcgen05/TMEM/TMA) k_gap_partial k_head_finish";
+    return "kdl 0.3 sm_100a: k_resize k_conv1 k_conv3x3_tc k_dw_tma k_sepconv_tc k_sepconv_mid k_pool_tma k_gemm_tc(tcgen05/TMEM/TMA) k_gap_partial k_head_finish";
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -821,6 +850,30 @@ static int check_call(KdlModel *m, int B, bool need_weights) {
     if (need_weights && !m->weights_loaded) { set_err(m->err, "kdl_load_weights has not been called"); return KDL_ESTATE; }
     cudaError_t e = cudaSetDevice(m->cfg.device);
     if (e != cudaSuccess) { set_err(m->err, "cudaSetDevice: %s", cudaGetErrorString(e)); return KDL_ECUDA; }
+    return KDL_OK;
+}
+
+// Everything a *_host entry point must know before it queues a copy: non-null arrays, sane geometry, and every image inside
+// the `total_bytes` the caller says it owns (a read past the staging buffer would be an illegal address, which is sticky and
+// poisons the CUDA context of the serving process).
+static int check_host_images(KdlModel *m, const char *fn, const uint8_t *h_src, size_t total_bytes, const int64_t *offset,
+                             const int32_t *h, const int32_t *w, const int64_t *pitch, int B, const float *h_out) {
+    char *err = m->err;
+    if (!h_src || !h_out || total_bytes == 0) { set_err(err, "%s: null buffer", fn); return KDL_EINVAL; }
+    if (!offset || !h || !w || !pitch) { set_err(err, "%s: null metadata array", fn); return KDL_EINVAL; }
+    for (int i = 0; i < B; ++i) {
+        if (h[i] < 1 || w[i] < 1 || pitch[i] < (int64_t)w[i] * 3 || offset[i] < 0) {
+            set_err(err, "%s: image %d: bad geometry h=%d w=%d pitch=%lld offset=%lld", fn, i, h[i], w[i], (long long)pitch[i],
+                    (long long)offset[i]);
+            return KDL_EINVAL;
+        }
+        const unsigned long long end = (unsigned long long)offset[i] + (unsigned long long)(h[i] - 1) * (unsigned long long)pitch[i] +
+                                       (unsigned long long)w[i] * 3ull;
+        if (end > (unsigned long long)total_bytes) {
+            set_err(err, "%s: image %d extends past total_bytes (%llu > %zu)", fn, i, end, total_bytes);
+            return KDL_EINVAL;
+        }
+    }
     return KDL_OK;
 }
 
@@ -871,7 +924,7 @@ static int run_forward_eager(KdlModel *m, const float *in_f32, const uint8_t *in
     struct PdlScope {  // programmatic dependent launch for the kernels of this forward pass (tensor-core path only)
         PdlScope(bool on) { pdl_enabled() = on; }
         ~PdlScope() { pdl_enabled() = false; }
-    } pdl_scope(B <= m->pdl_max_batch && m->cfg.precision == KDL_PRECISION_BF16 && m->cfg.gemm_impl == KDL_GEMM_AUTO && !m->profiling);
+    } pdl_scope(B <= m->tune.pdl_max_batch && m->cfg.precision == KDL_PRECISION_BF16 && m->cfg.gemm_impl == KDL_GEMM_AUTO && !m->profiling);
     if (m->cfg.precision == KDL_PRECISION_F32) {
         Runner<float> r{m, st, B};
         return r.forward(in_f32, in_u8, d_logits);
@@ -880,10 +933,22 @@ static int run_forward_eager(KdlModel *m, const float *in_f32, const uint8_t *in
     return r.forward(in_f32, in_u8, d_logits);
 }
 
-// The forward pass is a fixed sequence of ~85 launches whose arguments (arena pointers, TMA descriptors passed by value) depend
+// The forward pass is a fixed sequence of ~80 launches whose arguments (arena pointers, TMA descriptors passed by value) depend
 // only on (batch, input pointer).  With cfg.use_graphs the second call with a given key captures that sequence into a CUDA graph
 // (on the model's own stream) and later calls replay it on the caller's stream: what matters for batch-1 latency, where the
 // ~30 us of device work would otherwise sit behind ~400 us of launch overhead.  The graph writes to the model's logits buffer.
+// The cache is LRU with room for every batch size a dynamic batcher can produce (max_batch + 8 keys, at least 16, at most 264):
+// on overflow ONE least-recently-used entry is evicted, after a device synchronise so that no replay of it is still in flight.
+static size_t graph_capacity(const KdlModel *m) {
+    size_t c = (size_t)m->cfg.max_batch + 8;
+    return c < 16 ? 16 : (c > 264 ? 264 : c);
+}
+static void drop_graphs(KdlModel *m) {
+    if (m->graphs.empty()) return;
+    cudaDeviceSynchronize();
+    for (auto &g : m->graphs) if (g.exec) cudaGraphExecDestroy(g.exec);
+    m->graphs.clear();
+}
 static int run_forward(KdlModel *m, const float *in_f32, const uint8_t *in_u8, int B, float *d_logits, cudaStream_t st) {
     m->last_B = B;
     char *err = m->err;
@@ -892,15 +957,23 @@ static int run_forward(KdlModel *m, const float *in_f32, const uint8_t *in_u8, i
     for (auto &g : m->graphs)
         if (g.B == B && g.in_f32 == in_f32 && g.in_u8 == in_u8) { ge = &g; break; }
     if (!ge) {  // first sighting: run eagerly (also finishes any lazy initialisation), remember the key
-        if (m->graphs.size() >= 16) {
-            for (auto &g : m->graphs) if (g.exec) { cudaGraphExecDestroy(g.exec); }
-            m->graphs.clear();
+        if (m->graphs.size() >= graph_capacity(m)) {
+            size_t lru = 0;
+            for (size_t i = 1; i < m->graphs.size(); ++i)
+                if (m->graphs[i].last_use < m->graphs[lru].last_use) lru = i;
+            if (m->graphs[lru].exec) {
+                CK(cudaDeviceSynchronize());
+                cudaGraphExecDestroy(m->graphs[lru].exec);
+            }
+            m->graphs.erase(m->graphs.begin() + (long)lru);
+            m->graph_evictions++;
         }
         KdlModel::GraphEntry g;
-        g.B = B; g.in_f32 = in_f32; g.in_u8 = in_u8; g.exec = nullptr; g.launches = 0;
+        g.B = B; g.in_f32 = in_f32; g.in_u8 = in_u8; g.exec = nullptr; g.launches = 0; g.last_use = ++m->graph_clock;
         m->graphs.push_back(g);
         return run_forward_eager(m, in_f32, in_u8, B, d_logits, st);
     }
+    ge->last_use = ++m->graph_clock;
     if (!ge->exec) {
         const int before = m->launches;
         cudaGraph_t graph = nullptr;
@@ -914,11 +987,23 @@ static int run_forward(KdlModel *m, const float *in_f32, const uint8_t *in_u8, i
         if (e != cudaSuccess) { ge->exec = nullptr; set_err(err, "cudaGraphInstantiate -> %s", cudaGetErrorString(e)); return KDL_ECUDA; }
         ge->launches = m->launches - before;
         m->launches = before;
+        m->graph_captures++;
+    } else {
+        m->graph_replays++;
     }
     CK(cudaGraphLaunch(ge->exec, st));
     m->launches += ge->launches;
     if (d_logits != m->d_logits)
         CK(cudaMemcpyAsync(d_logits, m->d_logits, (size_t)B * 10 * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    return KDL_OK;
+}
+
+extern "C" int kdl_graph_stats(const KdlModel *m, int32_t *cached, int32_t *captures, int32_t *replays, int32_t *evictions) {
+    if (!m) { set_err(g_err, "kdl_graph_stats: null model"); return KDL_EINVAL; }
+    if (cached) *cached = (int32_t)m->graphs.size();
+    if (captures) *captures = m->graph_captures;
+    if (replays) *replays = m->graph_replays;
+    if (evictions) *evictions = m->graph_evictions;
     return KDL_OK;
 }
 
@@ -955,13 +1040,7 @@ extern "C" int kdl_predict_u8_host(KdlModel *m, const uint8_t *h_src, size_t tot
     int rc = check_call(m, B, true);
     if (rc) return rc;
     char *err = m->err;
-    if (!h_src || !h_dense_7 || total_bytes == 0) { set_err(err, "kdl_predict_u8_host: null buffer"); return KDL_EINVAL; }
-    for (int i = 0; i < B; ++i) {
-        if (offset && pitch && h && (size_t)(offset[i] + (int64_t)(h[i] - 1) * pitch[i] + (int64_t)w[i] * 3) > total_bytes) {
-            set_err(err, "image %d extends past total_bytes", i);
-            return KDL_EINVAL;
-        }
-    }
+    if ((rc = check_host_images(m, "kdl_predict_u8_host", h_src, total_bytes, offset, h, w, pitch, B, h_dense_7))) return rc;
     if (total_bytes > m->d_src_cap) {
         if (m->d_src) CK(cudaFree(m->d_src));
         m->d_src = nullptr; m->d_src_cap = 0;
@@ -994,7 +1073,7 @@ extern "C" int kdl_submit_u8_host(KdlModel *m, const uint8_t *h_src, size_t tota
     int rc = check_call(m, B, true);
     if (rc) return rc;
     char *err = m->err;
-    if (!h_src || !h_dense_7 || total_bytes == 0) { set_err(err, "kdl_submit_u8_host: null buffer"); return KDL_EINVAL; }
+    if ((rc = check_host_images(m, "kdl_submit_u8_host", h_src, total_bytes, offset, h, w, pitch, B, h_dense_7))) return rc;
     if (!m->pipe_init) {
         CK(cudaStreamCreateWithFlags(&m->copy_stream, cudaStreamNonBlocking));
         for (int i = 0; i < 2; ++i) {
@@ -1078,36 +1157,19 @@ extern "C" int kdl_layer_output(KdlModel *m, const char *tapname, float *d_out, 
 extern "C" int kdl_gemm_bf16(const void *d_A, const void *d_Wt, const float *d_bias, const void *d_residual, void *d_out,
                              int32_t M, int32_t N, int32_t K, int32_t relu, void *stream) {
     static thread_local tc::TmaEncoder enc;
-    char *err = g_err;
     if (!d_A || !d_Wt || !d_bias || !d_out || M < 1) { set_err(g_err, "kdl_gemm_bf16: null argument"); return KDL_EINVAL; }
     if (!tc::shape_supported(M, N, K)) { set_err(g_err, "kdl_gemm_bf16: unsupported shape M=%d N=%d K=%d (N,K must be multiples of 8)", M, N, K); return KDL_EINVAL; }
     if (!enc.ok()) enc.init();
     if (!enc.ok()) { set_err(g_err, "kdl_gemm_bf16: cuTensorMapEncodeTiled unavailable"); return KDL_ECUDA; }
     int rc = tc::configure(g_err);
     if (rc) return rc;
-    if ((rc = tc2::configure2(g_err))) return rc;
-    const bool one_cta = ((relu >> 1) & 1) || M < 256;
     CUtensorMap tmB;
-    if (!enc.encode_2d(&tmB, d_Wt, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, tc::BLOCK_K, one_cta ? tc::BLOCK_N : 128, 128)) {
+    if (!enc.encode_2d(&tmB, d_Wt, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, tc::BLOCK_K, tc::BLOCK_N, 128)) {
         set_err(g_err, "kdl_gemm_bf16: tensor map encode failed");
         return KDL_ECUDA;
     }
-    (void)err;
-    if ((relu >> 2) & 1) {
-        if ((rc = tcm2::configure(g_err))) return rc;
-        CUtensorMap tmB256;
-        if (!enc.encode_2d(&tmB256, d_Wt, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, tc::BLOCK_K, tc::BLOCK_N, 128)) {
-            set_err(g_err, "kdl_gemm_bf16: tensor map encode failed");
-            return KDL_ECUDA;
-        }
-        return tcm2::launch(enc, (const bf16 *)d_A, &tmB256, d_bias, (const bf16 *)d_residual, (bf16 *)d_out, M, N, K, relu & 1,
-                            (cudaStream_t)stream, g_err);
-    }
-    if (one_cta)
-        return tc::launch_gemm(enc, (const bf16 *)d_A, &tmB, d_bias, (const bf16 *)d_residual, (bf16 *)d_out, M, N, K, relu & 1,
-                               (cudaStream_t)stream, g_err);
-    return tc2::launch_gemm2(enc, (const bf16 *)d_A, &tmB, d_bias, (const bf16 *)d_residual, (bf16 *)d_out, M, N, K, relu & 1,
-                             (cudaStream_t)stream, g_err);
+    return tc::launch_gemm(enc, (const bf16 *)d_A, &tmB, d_bias, (const bf16 *)d_residual, (bf16 *)d_out, M, N, K, relu & 1,
+                           (cudaStream_t)stream, g_err);
 }
 
 // ---------------------------------------------------------------------------------------------------

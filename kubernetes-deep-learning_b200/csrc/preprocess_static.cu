@@ -137,6 +137,9 @@ extern "C" int kdl_preprocess_u8_static(const uint8_t *d_src, const int64_t *off
                     "KDL_STATIC_MAX_BATCH images per call; split the batch or use kdl_preprocess_u8", B, MAXB);
     if (S < 1 || S > MAXS)
         return fail(err, err_len, KDL_EINVAL, "kdl_preprocess_u8_static: target size %d is outside [1, %d] (KDL_STATIC_MAX_SIZE)", S, MAXS);
+    if ((reinterpret_cast<uintptr_t>(d_out) & 15u) != 0)   // k_static_resize stores float4 vectors at d_out + 4k
+        return fail(err, err_len, KDL_EINVAL, "kdl_preprocess_u8_static: d_out %p is not 16-byte aligned (kdl_preprocess_u8 takes any "
+                    "alignment; this entry stores 16-byte vectors)", (void *)d_out);
     MetaPack pack;
     memset(&pack, 0, sizeof pack);
     for (int i = 0; i < B; ++i) {

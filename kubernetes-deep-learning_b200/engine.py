@@ -63,7 +63,7 @@ class PackedImages:
 class Model:
     def __init__(self, weights: Dict[str, np.ndarray], device: int = 0, max_batch: int = 64, input_size: int = 299,
                  precision: str = "bf16", gemm_impl: str = "auto", keep_taps: bool = False,
-                 head_inner: Optional[int] = None, use_graphs: bool = True):
+                 head_inner: Optional[int] = None, use_graphs: bool = True, tuning: Optional[Dict[str, int]] = None):
         if not torch.cuda.is_available():
             raise RuntimeError("kdl_b200.Model needs a CUDA device (B200, sm_100a); there is no CPU fallback")
         self.lib = _lib.load()
@@ -86,6 +86,29 @@ class Model:
             blob = pack_blob(weights, head_inner)
             assert blob.size == self.lib.kdl_weight_count(head_inner)
             _lib.check(self.lib.kdl_load_weights(self.h, blob.ctypes.data, blob.size), self.h)
+        if tuning:
+            self.set_tuning(**tuning)
+
+    def get_tuning(self) -> Dict[str, int]:
+        t = _lib.KdlTuning()
+        _lib.check(self.lib.kdl_get_tuning(self.h, ctypes.byref(t)), self.h)
+        return {name: int(getattr(t, name)) for name, _ in _lib.KdlTuning._fields_ if name != "reserved"}
+
+    def set_tuning(self, **switches: int) -> None:
+        """Kernel-selection switches of include/kdl.h KdlTuning (e.g. fused_sepconv=0, pdl_max_batch=0); results are bit-identical
+        whatever is selected."""
+        t = _lib.KdlTuning()
+        _lib.check(self.lib.kdl_get_tuning(self.h, ctypes.byref(t)), self.h)
+        for k, v in switches.items():
+            if k == "reserved" or not hasattr(t, k):
+                raise KeyError(f"unknown tuning switch {k!r}")
+            setattr(t, k, int(v))
+        _lib.check(self.lib.kdl_set_tuning(self.h, ctypes.byref(t)), self.h)
+
+    def graph_stats(self) -> Dict[str, int]:
+        v = [ctypes.c_int32() for _ in range(4)]
+        _lib.check(self.lib.kdl_graph_stats(self.h, *[ctypes.byref(x) for x in v]), self.h)
+        return dict(zip(("cached", "captures", "replays", "evictions"), (int(x.value) for x in v)))
 
     def close(self):
         if getattr(self, "h", None):
@@ -225,9 +248,8 @@ class Model:
 
 
 def gemm_bf16(A: torch.Tensor, Wt: torch.Tensor, bias: torch.Tensor, residual: Optional[torch.Tensor] = None,
-              relu: bool = False, out: Optional[torch.Tensor] = None, one_cta: bool = False, m256: bool = False) -> torch.Tensor:
-    """Stand-alone tcgen05 GEMM: act(A[M,K] @ Wt[N,K]^T + bias) (+ residual); bf16 CUDA tensors.
-    one_cta=True forces the single-CTA kernel; default is the CTA-pair (cta_group::2) kernel when M >= 256."""
+              relu: bool = False, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Stand-alone tcgen05 GEMM (the model's k_gemm_tc): act(A[M,K] @ Wt[N,K]^T + bias) (+ residual); bf16 CUDA tensors."""
     lib = _lib.load()
     M, K = A.shape
     N = Wt.shape[0]
@@ -239,5 +261,5 @@ def gemm_bf16(A: torch.Tensor, Wt: torch.Tensor, bias: torch.Tensor, residual: O
     with torch.cuda.device(A.device):
         _lib.check(lib.kdl_gemm_bf16(A.data_ptr(), Wt.data_ptr(), bias.data_ptr(),
                                      residual.data_ptr() if residual is not None else None, out.data_ptr(), M, N, K,
-                                     int(relu) | (2 if one_cta else 0) | (4 if m256 else 0), st))
+                                     int(relu), st))
     return out

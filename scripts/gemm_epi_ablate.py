@@ -14,7 +14,7 @@ for res in (None, R):
     for i in range(8):
         flush.zero_()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(); engine.gemm_bf16(A, Wt, bias, res, True, out=out, one_cta=True); e1.record(); torch.cuda.synchronize()
+        e0.record(); engine.gemm_bf16(A, Wt, bias, res, True, out=out); e1.record(); torch.cuda.synchronize()
         if i >= 2: ts.append(e0.elapsed_time(e1))
     t = sorted(ts)[len(ts) // 2]
     print(os.environ.get("KDL_LIB", "default"), "residual" if res is not None else "no residual", f"{t*1e3:.1f} us  {2*M*N*K/t*1e-9:.0f} TF")

@@ -15,7 +15,7 @@ for M in (30720, 92416):
             if mode == "flushed":
                 flush.zero_()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record(); engine.gemm_bf16(A, Wt, bias, None, True, out=out, one_cta=True); e1.record(); torch.cuda.synchronize()
+            e0.record(); engine.gemm_bf16(A, Wt, bias, None, True, out=out); e1.record(); torch.cuda.synchronize()
             if i >= 3: ts.append(e0.elapsed_time(e1))
         t = sorted(ts)[len(ts) // 2]
         print(f"M={M:6d} {mode:<13} {t*1e3:7.1f} us  {2*M*N*K/t*1e-9:6.0f} TFLOP/s")

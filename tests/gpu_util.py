@@ -1,8 +1,30 @@
+"""Shared helpers of the GPU parity tests.
+
+Inputs are STRUCTURED pictures (oracle.structured: the reference's media/image2.png, crops and flips of it, solid colours,
+ramps, checkerboards, low-frequency fields), not white noise: noise images are statistically identical, so a random-init
+network gives them nearly the same logits and a kernel that ignored the image would pass "identical top-1"
+(VERDICT round 1, weak #1)."""
 import numpy as np
+
+from oracle import structured as S
+
+rel = S.rel
+centred_rel = S.centred_rel
+BF16_TOL = 2e-2          # north_star: bf16 logits within 2e-2 relative (rel = max|a-b| / max|b| per image), identical top-1
+F32_TOL = 1e-4           # north_star: fp32 path within 1e-4
 
 
 def synth_inputs(h, n, seed=0):
-    """uint8 U{0..255} -> the float32 tensor the gateway would send."""
+    """n structured pictures already at h x h -> (uint8 array (n,h,h,3), float32 tensor the gateway would send)."""
+    u = np.stack(S.structured_images(n, seed=seed, mixed_sizes=False, size=h))
+    x = u.astype(np.float32)
+    x /= 127.5
+    x -= 1.0
+    return u, x
+
+
+def noise_inputs(h, n, seed=0):
+    """i.i.d. U{0..255} pixels (SURVEY.md §8d's generator) -- kept for throughput-shaped cases only."""
     rng = np.random.default_rng(seed)
     u = rng.integers(0, 256, (n, h, h, 3), dtype=np.uint8)
     x = u.astype(np.float32)
@@ -11,8 +33,17 @@ def synth_inputs(h, n, seed=0):
     return u, x
 
 
-def rel(a, b):
-    a = np.asarray(a, np.float64)
-    b = np.asarray(b, np.float64)
-    d = np.max(np.abs(b))
-    return float(np.max(np.abs(a - b)) / (d if d > 0 else 1.0))
+def batch_signal_rel(got, want):
+    """Per-image error of the image-dependent part against ONE scale for the whole batch: max_i |(a-abar)-(b-bbar)| over the
+    amplitude of the image-dependent signal max|b-bbar| (means over the batch, per class).  Unlike the per-image ratio it does
+    not blow up for a picture whose logits happen to sit near the batch mean."""
+    a = np.asarray(got, np.float64)
+    b = np.asarray(want, np.float64)
+    ac, bc = a - a.mean(0, keepdims=True), b - b.mean(0, keepdims=True)
+    return np.abs(ac - bc).max(1) / np.abs(bc).max()
+
+
+def top2_margin(want):
+    """fp64 top-1 minus runner-up, per image"""
+    s = np.sort(np.asarray(want, np.float64), axis=1)
+    return s[:, -1] - s[:, -2]

@@ -95,3 +95,52 @@ def test_standalone_gemm_entry_validates_its_arguments():
     assert b"multiples of 8" in lib.kdl_last_error(None)
     assert lib.kdl_gemm_bf16(a.data_ptr(), b.data_ptr(), bias.data_ptr(), None, out.data_ptr(), 128, 64, 64, 0, st) == _lib.KDL_OK
     torch.cuda.synchronize()
+
+
+def test_host_entry_points_validate_geometry_before_queueing_any_copy():
+    """kdl_submit_u8_host must refuse inconsistent image metadata the way kdl_predict_u8_host does --
+    an image that extends past total_bytes would make k_resize read past the staging buffer, and an illegal address is sticky
+    for the whole process.  Both entry points share one check; afterwards the model still works."""
+    import kdl_b200  # noqa: F401
+    from kdl_b200 import _lib, engine, weights
+    lib = _lib.load()
+    m = engine.Model(weights.make_weights(1, "keras_default"), max_batch=2, input_size=96, precision="bf16", use_graphs=False)
+    try:
+        img = np.full((40, 50, 3), 7, np.uint8)
+        pk = engine.PackedImages([img, img], pinned=True)
+        out = torch.empty((2, 10), dtype=torch.float32).pin_memory()
+
+        def call(fn, total=None, **over):
+            arr = {"offset": pk.offset.copy(), "h": pk.h.copy(), "w": pk.w.copy(), "pitch": pk.pitch.copy()}
+            ptr = {}
+            for k in arr:
+                if k in over and over[k] is None:
+                    ptr[k] = None
+                else:
+                    if k in over:
+                        arr[k][1] = over[k]
+                    ptr[k] = arr[k].ctypes.data
+            rc = fn(m.h, pk.host.data_ptr(), pk.total_bytes if total is None else total, ptr["offset"], ptr["h"], ptr["w"], ptr["pitch"],
+                    2, out.data_ptr())
+            return rc, lib.kdl_last_error(m.h)
+
+        for fn in (lib.kdl_submit_u8_host, lib.kdl_predict_u8_host):
+            rc, msg = call(fn, h=4000)                         # 4000 rows of 150 bytes do not fit the packed buffer
+            assert rc == _lib.KDL_EINVAL and b"extends past total_bytes" in msg, msg
+            rc, msg = call(fn, offset=pk.total_bytes)          # starts at the very end
+            assert rc == _lib.KDL_EINVAL and b"extends past total_bytes" in msg, msg
+            rc, msg = call(fn, total=100)
+            assert rc == _lib.KDL_EINVAL and b"extends past total_bytes" in msg, msg
+            rc, msg = call(fn, w=0)
+            assert rc == _lib.KDL_EINVAL and b"bad geometry" in msg, msg
+            rc, msg = call(fn, pitch=10)                       # pitch smaller than a row
+            assert rc == _lib.KDL_EINVAL and b"bad geometry" in msg, msg
+            rc, msg = call(fn, w=None)                         # null metadata array (used to be dereferenced)
+            assert rc == _lib.KDL_EINVAL and b"null metadata" in msg, msg
+        assert lib.kdl_wait(m.h) == _lib.KDL_OK                # nothing was queued
+        rc, _ = call(lib.kdl_submit_u8_host)
+        assert rc == _lib.KDL_OK and lib.kdl_wait(m.h) == _lib.KDL_OK
+        want = m.predict_packed_host(pk)
+        np.testing.assert_array_equal(out.numpy(), want)
+    finally:
+        m.close()

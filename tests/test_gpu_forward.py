@@ -1,25 +1,30 @@
 """GPU parity of the Xception forward (through the C ABI) against the fp64 oracle.
 
 Tolerances (BASELINE.json north_star): rel = max|a-b| / max|b| per image;
-  fp32 path <= 1e-4;   bf16 path <= 2e-2 with identical top-1.  Layer-wise on the calibrated init, because
-  a logits-only check is blind to the middle flow under Keras-default init.
+  fp32 path <= 1e-4;   bf16 path <= 2e-2 with identical top-1.  Layer-wise as well, because a logits-only check is blind
+  to the middle flow under Keras-default init.
 
-bf16 note.  On the reference's own random init (Keras defaults) the bf16 path sits at 3e-3, far inside 2e-2.  The calibrated
-init is deliberately hostile (every branch as large as its skip path, activations growing x2 per block): there the per-image
-error is a random variable with mean ~1.2e-2 whose tail crosses 2e-2 for roughly one image in ten (bf16 weight
-rounding dominates and does not average out).  The test therefore asserts 2e-2 on the MEAN over the batch and 3e-2 on every
-image for that init, and the strict per-image 2e-2 + identical top-1 on the Keras-default init; top-1 on the calibrated init
-may differ only where the fp64 top-2 margin is itself inside the error bound."""
+Inputs are structured pictures (tests/gpu_util.py) and the head biases are re-centred on the batch
+(oracle.structured.recentre_head), so the logits are dominated by what distinguishes the pictures and the batch spans
+several argmax classes: the tests assert that the fp64 oracle itself sees >= 4 different classes, which makes
+"identical top-1" a statement about the image-dependent signal.
+
+What the bf16 path is held to, per init (measured numbers: BASELINE.md §5):
+  * keras_default (the reference's own random init) and calibrated_mild (every layer matters, residual branches are
+    corrections to the skip path as in a trained network): the north_star contract literally -- every image <= 2e-2 on the
+    init's natural head, identical top-1.
+  * every init, re-centred head: identical top-1 on every picture whose fp64 top-2 margin exceeds the bf16 error bound, and
+    the error of the image-dependent part <= 2e-2 of the batch's signal amplitude (gpu_util.batch_signal_rel).
+  * calibrated (deliberately hostile: the residual stream doubles in variance per block, so every rounding error reaches
+    the logits undamped; oracle/bf16_model.py reproduces its error on the CPU and shows that bf16 WEIGHT rounding is 85 % of
+    it): mean <= 2e-2 and every image <= 3e-2 on the natural head -- the accepted deviation, recorded with its p95 / max."""
 import numpy as np
 import pytest
 import torch
 
-from gpu_util import rel, synth_inputs
+from gpu_util import BF16_TOL, F32_TOL, batch_signal_rel, rel, synth_inputs, top2_margin
 
 pytestmark = pytest.mark.gpu
-
-F32_TOL = 1e-4
-BF16_TOL = 2e-2
 
 
 def _oracle(W, x, taps=None):
@@ -63,27 +68,31 @@ def test_fp32_path_logits_and_layers(h, init):
 
 
 @pytest.mark.parametrize("gemm", ["simple", "auto"])
-@pytest.mark.parametrize("h,init", [(299, "calibrated"), (150, "calibrated"), (299, "keras_default")])
+@pytest.mark.parametrize("h,init", [(299, "calibrated"), (150, "calibrated"), (299, "keras_default"), (299, "calibrated_mild"),
+                                    (150, "calibrated_mild")])
 def test_bf16_path_logits_top1_and_layers(h, init, gemm):
     from kdl_b200 import weights
+    from oracle import structured as S
     W = weights.make_weights(1, init)
-    n = 8
+    n = 16
     _, x = synth_inputs(h, n)
     taps = {}
     want = _oracle(W, x, taps)
+    # the same network with the head re-centred on this batch: the discriminating variant
+    Wc = S.recentre_head(W, taps["avg_pool"])
+    want_c = S.head_only(Wc, taps["avg_pool"])
+    if init != "keras_default":                      # (Keras-default logits are ~1e-5: its argmax is the same for every picture)
+        assert len(set(want_c.argmax(1).tolist())) >= 4, want_c.argmax(1)
+
     m = _mk(W, max_batch=n, input_size=h, precision="bf16", gemm_impl=gemm, keep_taps=True)
     try:
         got = m.serving_default(input_8=x)["dense_7"]
-        errs = [rel(got[i], want[i]) for i in range(n)]
-        if init == "keras_default":
-            assert max(errs) <= BF16_TOL, errs
+        errs = np.array([rel(got[i], want[i]) for i in range(n)])
+        if init == "calibrated":                     # hostile init: the accepted deviation
+            assert float(errs.mean()) <= BF16_TOL and float(errs.max()) <= 1.5 * BF16_TOL, errs
+        else:                                        # the contract, literally
+            assert float(errs.max()) <= BF16_TOL, errs
             assert (got.argmax(1) == want.argmax(1)).all()
-        else:
-            assert float(np.mean(errs)) <= BF16_TOL and max(errs) <= 1.5 * BF16_TOL, errs
-            for i in range(n):
-                if got[i].argmax() != want[i].argmax():      # only allowed on a near-tie of the fp64 logits
-                    top2 = np.sort(want[i])[-2:]
-                    assert top2[1] - top2[0] <= BF16_TOL * np.abs(want[i]).max(), (i, want[i], got[i])
         worst = 0.0
         for name in m.tap_names():
             a, relu = m.layer_output(name)
@@ -95,11 +104,26 @@ def test_bf16_path_logits_top1_and_layers(h, init, gemm):
             worst = max(worst, e)
             # per-layer drift stays within the end-to-end bf16 budget (keras_default branches are ~1e-6 of the
             # skip path, so only their block outputs are meaningful there)
-            if init == "calibrated" or name.endswith("_out") or name.startswith("block1"):
+            if init != "keras_default" or name.endswith("_out") or name.startswith("block1"):
                 assert e <= 1.5 * BF16_TOL, (name, e)
-        print(f"bf16 {gemm} h={h} {init}: logits rel {max(errs):.2e}, worst layer rel {worst:.2e}")
     finally:
         m.close()
+
+    mc = _mk(Wc, max_batch=n, input_size=h, precision="bf16", gemm_impl=gemm)
+    try:
+        got_c = mc.serving_default(input_8=x)["dense_7"]
+    finally:
+        mc.close()
+    sig = batch_signal_rel(got_c, want_c)
+    assert float(sig.max()) <= BF16_TOL, sig
+    # identical top-1 wherever the fp64 margin is larger than the error the path is allowed to have
+    bound = BF16_TOL * np.abs(want_c - want_c.mean(0, keepdims=True)).max()
+    decided = top2_margin(want_c) > 2 * bound
+    if init != "keras_default":
+        assert decided.sum() >= n // 2, top2_margin(want_c)
+    assert (got_c.argmax(1)[decided] == want_c.argmax(1)[decided]).all(), (got_c.argmax(1), want_c.argmax(1))
+    print(f"bf16 {gemm} h={h} {init}: natural head rel mean {errs.mean():.2e} max {errs.max():.2e}; re-centred head signal err "
+          f"max {sig.max():.2e}, top-1 {got_c.argmax(1).tolist()} ({int(decided.sum())}/{n} decided); worst layer {worst:.2e}")
 
 
 def test_fused_uint8_path_matches_two_step():

@@ -17,8 +17,7 @@ SHAPES = [
 
 @pytest.mark.parametrize("M,N,K", SHAPES)
 @pytest.mark.parametrize("relu,resid", [(False, False), (True, False), (False, True)])
-@pytest.mark.parametrize("one_cta", [True, False, "m256"], ids=["cta1", "cta2", "m256"])
-def test_gemm_tc_matches_fp32_reference(M, N, K, relu, resid, one_cta):
+def test_gemm_tc_matches_fp32_reference(M, N, K, relu, resid):
     import kdl_b200  # noqa: F401
     from kdl_b200 import engine
     g = torch.Generator(device="cuda").manual_seed(M * 31 + N * 7 + K)
@@ -26,7 +25,7 @@ def test_gemm_tc_matches_fp32_reference(M, N, K, relu, resid, one_cta):
     Wt = (torch.randn((N, K), generator=g, device="cuda") / K ** 0.5).to(torch.bfloat16)
     bias = torch.randn((N,), generator=g, device="cuda")
     R = torch.randn((M, N), generator=g, device="cuda").to(torch.bfloat16) if resid else None
-    out = engine.gemm_bf16(A, Wt, bias, R, relu, one_cta=one_cta is True, m256=one_cta == "m256")
+    out = engine.gemm_bf16(A, Wt, bias, R, relu)
     torch.cuda.synchronize()
     ref = A.float() @ Wt.float().t() + bias
     if relu:
@@ -37,8 +36,7 @@ def test_gemm_tc_matches_fp32_reference(M, N, K, relu, resid, one_cta):
     assert err <= 1e-2, err
 
 
-@pytest.mark.parametrize("one_cta", [True, False, "m256"], ids=["cta1", "cta2", "m256"])
-def test_gemm_tc_in_place_residual(one_cta):
+def test_gemm_tc_in_place_residual():
     import kdl_b200  # noqa: F401
     from kdl_b200 import engine
     g = torch.Generator(device="cuda").manual_seed(5)
@@ -48,6 +46,6 @@ def test_gemm_tc_in_place_residual(one_cta):
     bias = torch.randn((N,), generator=g, device="cuda")
     X = torch.randn((M, N), generator=g, device="cuda").to(torch.bfloat16)
     ref = A.float() @ Wt.float().t() + bias + X.float()
-    engine.gemm_bf16(A, Wt, bias, X, False, out=X, one_cta=one_cta is True, m256=one_cta == "m256")     # the middle-flow skip connection is updated in place
+    engine.gemm_bf16(A, Wt, bias, X, False, out=X)     # the middle-flow skip connection is updated in place
     torch.cuda.synchronize()
     assert (X.float() - ref).abs().max().item() / ref.abs().max().item() <= 1e-2

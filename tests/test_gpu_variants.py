@@ -1,8 +1,6 @@
-"""Kernel-selection variants of the bf16 path must agree: the fused depthwise+pointwise kernel vs. separate kernels, the three
-tensor-core GEMM tilings, the two conv2 formulations.  They perform the same arithmetic in the same order, so the logits are
+"""Kernel-selection variants of the bf16 path (include/kdl.h KdlTuning) must agree: the fused depthwise+pointwise kernel vs.
+separate kernels, the two conv2 formulations, programmatic dependent launch, tile order, the depthwise store path.  They perform the same arithmetic in the same order, so the logits are
 compared exactly; odd input sizes exercise every tile-edge path against the oracle."""
-import os
-
 import numpy as np
 import pytest
 import torch
@@ -12,20 +10,12 @@ from gpu_util import rel, synth_inputs
 pytestmark = pytest.mark.gpu
 
 
-def _logits(env, W, u8, size=299):
+def _logits(tuning, W, u8, size=299):
     import kdl_b200  # noqa: F401
     from kdl_b200 import engine
-    old = {k: os.environ.get(k) for k in env}
-    os.environ.update(env)
+    m = engine.Model(W, max_batch=len(u8), input_size=size, precision="bf16", use_graphs=False, tuning=tuning)
     try:
-        m = engine.Model(W, max_batch=len(u8), input_size=size, precision="bf16", use_graphs=False)   # env is read at kdl_create
-    finally:
-        for k, v in old.items():
-            if v is None:
-                os.environ.pop(k, None)
-            else:
-                os.environ[k] = v
-    try:
+        assert all(m.get_tuning()[k] == v for k, v in tuning.items())
         return m.predict_uint8(list(u8))
     finally:
         m.close()
@@ -33,13 +23,15 @@ def _logits(env, W, u8, size=299):
 
 def test_kernel_variants_are_bit_identical():
     from kdl_b200 import weights
+    from oracle import structured as S
     W = weights.make_weights(1, "calibrated")
-    u8, _ = synth_inputs(299, 5)
+    u8 = S.structured_images(5, mixed_sizes=False)
     base = _logits({}, W, u8)
-    for env in ({"KDL_NO_FUSED_SEPCONV": "1"}, {"KDL_GEMM_VARIANT": "2"}, {"KDL_GEMM_VARIANT": "3"}, {"KDL_CONV2_TAPS": "1"},
-                {"KDL_MICROBATCH_MB": "8"}, {"KDL_PDL": "1"}):
-        got = _logits(env, W, u8)
-        np.testing.assert_array_equal(got, base, err_msg=str(env))
+    assert len({tuple(r) for r in base.round(3).tolist()}) == 5          # five pictures, five different answers
+    for tuning in ({"fused_sepconv": 0}, {"conv2_shifted_taps": 1}, {"pdl_max_batch": 1 << 20}, {"pdl_max_batch": 0},
+                   {"serpentine": 0}, {"dw_direct_store": 1}, {"fused_midflow": 0}, {"fused_midflow": 0, "fused_sepconv": 0}):
+        got = _logits(tuning, W, u8)
+        np.testing.assert_array_equal(got, base, err_msg=str(tuning))
 
 
 def test_cuda_graph_replay_equals_eager():
@@ -113,19 +105,29 @@ def test_batch_one_and_full_batch_agree():
 
 def test_metric_batch_256_is_position_independent_and_matches_small_batches():
     """The metric's own configuration (batch 256 @299, BASELINE.json): the oracle cannot finish 256 images in seconds, so the full
-    size is pinned through properties.  A 256-batch is assembled from 8 distinct source images (different sizes, so the resize
-    runs for real) repeated 32 times in a shuffled order.  (1) every copy of an image gets bit-identical logits wherever it sits
-    in the batch (all 722 M tiles, every SM, both traversal directions); (2) they equal the logits of the same 8 images run as a
-    batch of 8 (small-M tiling, programmatic dependent launch) bit for bit; (3) those 8 agree with the fp64 oracle."""
+    size is pinned through properties.  A 256-batch is assembled from 8 distinct structured pictures (different sizes, so the
+    resize runs for real) repeated 32 times in a shuffled order.  (1) every copy of a picture gets bit-identical logits wherever
+    it sits in the batch (all 722 M tiles, every SM, both traversal directions); (2) they equal the logits of the same 8
+    pictures run as a batch of 8 (small-M tiling, programmatic dependent launch) bit for bit; (3) those 8 satisfy the north_star
+    contract against the fp64 oracle -- every image <= 2e-2 with identical top-1 (calibrated_mild init, natural head) -- and under
+    the re-centred head the 8 pictures land in >= 4 classes which the GPU reproduces."""
     import kdl_b200  # noqa: F401
+    from gpu_util import BF16_TOL, batch_signal_rel
     from kdl_b200 import engine, weights
     from oracle import preprocess_oracle as po
+    from oracle import structured as S
     from oracle import xception_oracle as xo
-    W = weights.make_weights(1, "calibrated")
+    W = weights.make_weights(1, "calibrated_mild")
     rng = np.random.default_rng(77)
-    srcs = [rng.integers(0, 256, (int(h), int(w), 3), dtype=np.uint8)
-            for h, w in ((299, 299), (534, 400), (64, 64), (1000, 37), (300, 298), (150, 150), (299, 640), (720, 1280))]
+    pics = S.structured_images(16)
+    srcs = [pics[i] for i in (0, 3, 5, 6, 8, 10, 12, 14)]          # photo, crop, white, red, ramp, checkerboard, 2 smooth fields
     order = rng.permutation(np.repeat(np.arange(8), 32))
+    x = np.concatenate([po.preprocess_pillow(s) for s in srcs])
+    taps = {}
+    want = xo.forward(W, x, torch.float64, taps)
+    Wc = S.recentre_head(W, taps["avg_pool"])
+    want_c = S.head_only(Wc, taps["avg_pool"])
+    assert len(set(want_c.argmax(1).tolist())) >= 4, want_c.argmax(1)
     m = engine.Model(W, max_batch=256, precision="bf16")
     try:
         big = m.predict_uint8([srcs[i] for i in order])
@@ -137,8 +139,89 @@ def test_metric_batch_256_is_position_independent_and_matches_small_batches():
     for pos, i in enumerate(order):
         np.testing.assert_array_equal(big[pos], small[i], err_msg=f"position {pos} image {i}")
     np.testing.assert_array_equal(again, big)
-    x = np.concatenate([po.preprocess_pillow(s) for s in srcs])
+    errs = [rel(small[i], want[i]) for i in range(8)]
+    assert max(errs) <= BF16_TOL, errs
+    assert small.argmax(1).tolist() == want.argmax(1).tolist()
+    mc = engine.Model(Wc, max_batch=256, precision="bf16")
+    try:
+        big_c = mc.predict_uint8([srcs[i] for i in order])
+    finally:
+        mc.close()
+    first = [int(np.flatnonzero(order == i)[0]) for i in range(8)]
+    got_c = big_c[first]
+    assert float(batch_signal_rel(got_c, want_c).max()) <= BF16_TOL
+    assert got_c.argmax(1).tolist() == want_c.argmax(1).tolist()
+
+
+def test_small_input_variant_batch_256_properties():
+    """BASELINE.json configs[2]: 150x150 at batch 256 (spatial chain 74/72/36/18/9/5: the (0,1) pool padding everywhere and the
+    tiny-M GEMM tiles).  Same property test as at 299: 8 structured pictures x 32 shuffled copies are position-independent, equal
+    the batch-of-8 result bit for bit, and the 8 meet the contract against the fp64 oracle."""
+    import kdl_b200  # noqa: F401
+    from gpu_util import BF16_TOL
+    from kdl_b200 import engine, weights
+    from oracle import preprocess_oracle as po
+    from oracle import structured as S
+    from oracle import xception_oracle as xo
+    W = weights.make_weights(1, "calibrated_mild")
+    rng = np.random.default_rng(78)
+    pics = S.structured_images(16)
+    srcs = [pics[i] for i in (1, 2, 4, 7, 9, 11, 13, 15)]
+    order = rng.permutation(np.repeat(np.arange(8), 32))
+    m = engine.Model(W, max_batch=256, input_size=150, precision="bf16")
+    try:
+        big = m.predict_uint8([srcs[i] for i in order])
+        small = m.predict_uint8(srcs)
+    finally:
+        m.close()
+    for pos, i in enumerate(order):
+        np.testing.assert_array_equal(big[pos], small[i], err_msg=f"position {pos} image {i}")
+    x = np.concatenate([po.preprocess_pillow(s, 150, 150) for s in srcs])
     want = xo.forward(W, x, torch.float64)
     errs = [rel(small[i], want[i]) for i in range(8)]
-    assert max(errs) <= 3e-2 and float(np.mean(errs)) <= 2e-2, errs
-    assert [int(np.argmax(small[i])) for i in range(8)] == [int(np.argmax(want[i])) for i in range(8)] or max(errs) <= 2e-2
+    assert max(errs) <= BF16_TOL, errs
+    assert small.argmax(1).tolist() == want.argmax(1).tolist()
+
+
+def test_graph_cache_keeps_replaying_under_a_dynamic_batcher():
+    """the batcher of the shipped deployment (max_batch_size 32) produces every batch size 1..32; the CUDA-graph
+    cache must hold them all (LRU, max_batch + 8 keys) instead of clearing itself on the 17th.  Cycle B = 1..32 three times
+    through Gateway's uint8 path: pass 1 runs eagerly, pass 2 captures, pass 3 must be 32 replays with no eviction."""
+    import kdl_b200  # noqa: F401
+    from kdl_b200 import engine, gateway, weights
+    from oracle import structured as S
+    W = weights.make_weights(1, "keras_default")
+    m = engine.Model(W, max_batch=32, input_size=96, precision="bf16", use_graphs=True)
+    g = gateway.Gateway(m)
+    pics = S.structured_images(32, mixed_sizes=False, size=96)
+    try:
+        ref = {}
+        for rnd in range(3):
+            before = m.graph_stats()
+            for b in range(1, 33):
+                y = np.stack(g._run_u8(pics[:b]))
+                if rnd == 0:
+                    ref[b] = y
+                else:
+                    np.testing.assert_array_equal(y, ref[b])       # eager, captured and replayed passes agree bit for bit
+            after = m.graph_stats()
+            if rnd == 1:
+                assert after["captures"] - before["captures"] == 32
+            if rnd == 2:
+                assert after["replays"] - before["replays"] == 32 and after["captures"] == before["captures"]
+        st = m.graph_stats()
+        assert st["evictions"] == 0 and st["cached"] == 32
+        # overflow evicts ONE least-recently-used entry, not the whole cache
+        m2 = engine.Model(W, max_batch=4, input_size=96, precision="bf16", use_graphs=True)     # capacity 16 keys
+        try:
+            x = torch.zeros((4, 96, 96, 3), device="cuda")
+            bufs = [x.clone() for _ in range(18)]                   # (batch, input pointer) is the key: 18 distinct keys
+            for t in bufs:
+                m2.forward_device(t[:1])
+            s2 = m2.graph_stats()
+            assert s2["cached"] == 16 and s2["evictions"] == 2
+        finally:
+            m2.close()
+    finally:
+        g.close()
+        m.close()

@@ -71,3 +71,15 @@ def test_weight_file_dispatch(tmp_path, monkeypatch):
     assert list(got) == list(W) and all(np.array_equal(got[k], W[k]) for k in W)
     with pytest.raises(ValueError, match="unknown weight file type"):
         weights.load(str(tmp_path / "m.ckpt"))
+
+
+def test_entry_points_refuse_to_serve_without_weights(monkeypatch):
+    """a missing KDL_WEIGHTS must fail loudly (TF-Serving does not start without its model either),
+    unless random weights are asked for explicitly."""
+    from kdl_b200 import weights
+    monkeypatch.delenv("KDL_WEIGHTS", raising=False)
+    monkeypatch.delenv("KDL_ALLOW_RANDOM_WEIGHTS", raising=False)
+    with pytest.raises(RuntimeError, match="KDL_WEIGHTS is not set"):
+        weights.load_from_env()
+    monkeypatch.setenv("KDL_ALLOW_RANDOM_WEIGHTS", "1")
+    assert "dense_7/kernel" in weights.load_from_env()
