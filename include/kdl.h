@@ -61,10 +61,10 @@ typedef struct KdlTuning {
                                     rows its producer wrote last (activations exceed the 126 MB L2 at large batch) */
     int32_t conv2_shifted_taps;  /* !=0: block1_conv2 as 9 shifted TMA boxes per tile instead of the staged halo (default 0) */
     int32_t fused_sepconv;       /* !=0 (default): blocks 2-3 run the fused depthwise+pointwise kernel */
-    int32_t dw_direct_store;     /* !=0: depthwise kernels store straight from registers instead of smem + TMA store (default 0) */
-    int32_t fused_midflow;       /* !=0 (default): 728 -> 728 layers at 19 x 19 (middle flow, block13_sepconv1) run the fused
-                                    depthwise+pointwise kernel with flat-pixel tiles (sepconv_mid.cuh) */
-    int32_t reserved[6];         /* must be 0 */
+    int32_t fused_midflow;       /* !=0: 728 -> 728 layers at 19 x 19 (middle flow, block13_sepconv1) run the fused depthwise+pointwise
+                                    kernel with flat-pixel tiles (sepconv_mid.cuh).  Default 0: it is bit-identical but measured
+                                    slower than k_dw_tma + k_gemm_tc on a B200 (DESIGN.md §4 has the cycle breakdown) */
+    int32_t reserved[7];         /* must be 0 */
 } KdlTuning;
 int kdl_get_tuning(const KdlModel *m, KdlTuning *out);
 int kdl_set_tuning(KdlModel *m, const KdlTuning *t);

@@ -197,7 +197,7 @@ static KdlTuning default_tuning() {
     t.serpentine = 1;
     t.conv2_shifted_taps = 0;
     t.fused_sepconv = 1;
-    t.fused_midflow = 1;
+    t.fused_midflow = 0;   // built, bit-identical, measured: 246 us per 728->728 layer at batch 256 against 165 us for k_dw_tma + k_gemm_tc
     return t;
 }
 
@@ -1222,3 +1222,10 @@ extern "C" int kdl_profile_end(KdlModel *m, KdlProfileRow *rows, int32_t capacit
     m->ev_used = 0;
     return KDL_OK;
 }
+
+#ifdef KDL_MID_PROF
+// probe builds only (make prof): cycle counters of the last k_sepconv_mid launch, [ctas][32]
+extern "C" int kdl_mid_prof_read(unsigned long long *out, int ctas) {
+    return cudaMemcpyFromSymbol(out, kdl::sepm::g_mid_prof, sizeof(unsigned long long) * 32 * (size_t)ctas) == cudaSuccess ? 0 : -2;
+}
+#endif

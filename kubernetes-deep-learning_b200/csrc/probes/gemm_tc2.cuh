@@ -77,6 +77,19 @@ __device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
                  : "memory");
 }
 
+#ifdef KDL_PAIR_PROF
+__device__ unsigned long long g_pair_prof[160][16];
+#define PP_T0() long long pp_t0 = clock64()
+#define PP_ADD(var) do { long long pp_t1 = clock64(); var += pp_t1 - pp_t0; pp_t0 = pp_t1; } while (0)
+#define PP_DECL(...) long long __VA_ARGS__
+#define PP_STORE(idx, v) g_pair_prof[blockIdx.x][idx] = (unsigned long long)(v)
+#else
+#define PP_T0()
+#define PP_ADD(var)
+#define PP_DECL(...)
+#define PP_STORE(idx, v)
+#endif
+
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
 k_gemm_tc2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmOut,
            const float *__restrict__ bias, const bf16 *residual, int M, int N, int K, int relu, int ldo) {
@@ -122,13 +135,18 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
+            PP_DECL(w_e = 0, w_i = 0);
+            PP_T0();
+            const long long t_begin = clock64();
             for (int tile = cluster_id; tile < num_tiles; tile += n_clusters) {
                 const int m0 = (tile / n_tiles) * 256 + (int)rank * 128;
                 const int n0 = (tile % n_tiles) * BN2;
                 const int n_inst = (min(BN2, N - n0) + 15) & ~15;           // instruction N; each CTA supplies n_inst/2 weight rows
                 const int nb0 = n0 + (int)rank * (n_inst >> 1);
                 for (int kb = 0; kb < k_blocks; ++kb) {
+                    PP_ADD(w_i);
                     mbar_wait(empty_bar(stage), phase ^ 1u);
+                    PP_ADD(w_e);
                     const uint32_t lfull = map_to_cta(full_bar(stage), 0);
                     if (leader) mbar_expect_tx(full_bar(stage), 2 * STAGE2_BYTES);
                     const uint32_t sa = smem_base + stage * STAGE2_BYTES;
@@ -137,6 +155,8 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
                     if (++stage == STAGES2) { stage = 0; phase ^= 1u; }
                 }
             }
+            PP_ADD(w_i);
+            PP_STORE(0, w_e); PP_STORE(1, w_i); PP_STORE(7, clock64() - t_begin);
         }
     } else if (warp == 1) {
         // ================= MMA issuer (leader CTA only) =================
@@ -144,17 +164,23 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
+            PP_DECL(w_te = 0, w_f = 0, w_i = 0);
+            PP_T0();
             for (int tile = cluster_id; tile < num_tiles; tile += n_clusters, ++it) {
                 const int n0 = (tile % n_tiles) * BN2;
                 const int acc = it & 1;
                 const uint32_t acc_phase = (it >> 1) & 1;
                 const int n_inst = (min(BN2, N - n0) + 15) & ~15;
                 const uint32_t idesc = make_idesc(256, (uint32_t)n_inst);
+                PP_ADD(w_i);
                 mbar_wait(tempty_bar(acc), acc_phase ^ 1u);  // both CTAs' epilogues have drained this accumulator
+                PP_ADD(w_te);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * BN2;
                 for (int kb = 0; kb < k_blocks; ++kb) {
+                    PP_ADD(w_i);
                     mbar_wait(full_bar(stage), phase);
+                    PP_ADD(w_f);
                     tc_fence_after();
                     const uint32_t sa = smem_base + stage * STAGE2_BYTES;
                     const uint64_t adesc = make_smem_desc<128>(sa);
@@ -167,6 +193,8 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
                 }
                 umma_commit_pair(tfull_bar(acc));
             }
+            PP_ADD(w_i);
+            PP_STORE(2, w_te); PP_STORE(3, w_f); PP_STORE(4, w_i);
         }
     } else {
         // ================= epilogue: warps 2..5 of both CTAs, each CTA drains its own 128 accumulator rows =================
@@ -176,6 +204,8 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
         const bool has_res = residual != nullptr;
         int staged_n0 = -1;
         int it = 0;
+        PP_DECL(w_tf = 0, w_w = 0);
+        PP_T0();
         for (int tile = cluster_id; tile < num_tiles; tile += n_clusters, ++it) {
             const int m0 = (tile / n_tiles) * 256 + (int)rank * 128;
             const int n0 = (tile % n_tiles) * BN2;
@@ -204,7 +234,9 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
                 }
             };
             if (has_res) load_res(0);
+            PP_ADD(w_w);
             mbar_wait(tfull_bar(acc), acc_phase);
+            PP_ADD(w_tf);
             tc_fence_after();
 #pragma unroll
             for (int c = 0; c < BN2 / 64; ++c) {
@@ -239,6 +271,8 @@ k_gemm_tc2(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUte
             if (lane == 0) mbar_arrive_cluster(map_to_cta(tempty_bar(acc), 0));
         }
         if (lane == 0) bulk_wait_all<0>();
+        PP_ADD(w_w);
+        if (warp == 2 && lane == 0) { PP_STORE(5, w_tf); PP_STORE(6, w_w); }
     }
     tc_fence_before();
     cluster_sync_all();  // nobody leaves while the peer may still signal its barriers / read its shared memory

@@ -66,31 +66,53 @@ __device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap *tm,
         : "memory");
 }
 
-// dw_tma.cuh's scatter_row with run-time (warp-uniform) switches: the rows of a flat-pixel tile that belong to the neighbouring
-// image must not contribute (they sit where the SAME padding's zero row would be).  Same operations in the same order per output.
-template <bool RELU>
-__device__ __forceinline__ void scatter_row_masked(uint32_t rowaddr, const float2 (&wl)[9], const float2 (&wh)[9], float2 (&aA)[2][2],
-                                                   float2 (&aB)[2][2], float2 (&aC)[2][2], bool do_a, bool do_b, bool do_c) {
-    dwt::Px in[4];
+// One staged input row of a depthwise thread: 4 adjacent pixels x 4 channels, still packed bf16 (8 registers).  Loading the NEXT row's
+// Raw before the current row is processed is what hides the shared-memory latency: only 10 depthwise warps run per SM here.
+struct Raw {
+    uint32_t v[8];
+};
+__device__ __forceinline__ Raw load_raw(uint32_t rowaddr) {
+    Raw r;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) in[j] = dwt::ld_px<RELU>(rowaddr + 128u * j);
+    for (int j = 0; j < 4; ++j)
+        asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(r.v[2 * j]), "=r"(r.v[2 * j + 1]) : "r"(rowaddr + 128u * j));
+    return r;
+}
+template <bool RELU> __device__ __forceinline__ void unpack_raw(const Raw &r, dwt::Px (&in)[4]) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        uint32_t a = r.v[2 * j], b = r.v[2 * j + 1];
+        if (RELU) {  // packed bf16x2 max against +0
+            asm("max.bf16x2 %0, %0, %1;" : "+r"(a) : "r"(0u));
+            asm("max.bf16x2 %0, %0, %1;" : "+r"(b) : "r"(0u));
+        }
+        in[j].lo = make_float2(__uint_as_float(a << 16), __uint_as_float(a & 0xffff0000u));
+        in[j].hi = make_float2(__uint_as_float(b << 16), __uint_as_float(b & 0xffff0000u));
+    }
+}
+// dw_tma.cuh's scatter_row on already unpacked pixels: bottom taps (ky = 2) complete the output row above (aA), middle taps go to
+// the row itself (aB), top taps open the row below (aC; zero when the row below belongs to the next image).  Same operations in
+// the same order per output as k_dw_tma.
+template <bool DO_A, bool DO_B, bool DO_C>
+__device__ __forceinline__ void scatter_px(const dwt::Px (&in)[4], const float2 (&wl)[9], const float2 (&wh)[9], float2 (&aA)[2][2],
+                                           float2 (&aB)[2][2], float2 (&aC)[2][2]) {
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
-        if (do_a) {
+        if (DO_A) {
 #pragma unroll
             for (int kx = 0; kx < 3; ++kx) {
                 aA[j][0] = ffma2(in[j + kx].lo, wl[6 + kx], aA[j][0]);
                 aA[j][1] = ffma2(in[j + kx].hi, wh[6 + kx], aA[j][1]);
             }
         }
-        if (do_b) {
+        if (DO_B) {
 #pragma unroll
             for (int kx = 0; kx < 3; ++kx) {
                 aB[j][0] = ffma2(in[j + kx].lo, wl[3 + kx], aB[j][0]);
                 aB[j][1] = ffma2(in[j + kx].hi, wh[3 + kx], aB[j][1]);
             }
         }
-        if (do_c) {
+        if (DO_C) {
             float2 cl = dwt::fmul2(in[j].lo, wl[0]), ch = dwt::fmul2(in[j].hi, wh[0]);
 #pragma unroll
             for (int kx = 1; kx < 3; ++kx) {
@@ -105,6 +127,20 @@ __device__ __forceinline__ void scatter_row_masked(uint32_t rowaddr, const float
         }
     }
 }
+
+// -DKDL_MID_PROF (probe builds only): per-role wait / work cycle counters of the last launch, one row per CTA
+#ifdef KDL_MID_PROF
+__device__ unsigned long long g_mid_prof[160][32];
+#define MP_T0() long long mp_t0 = clock64()
+#define MP_ADD(var) do { long long mp_t1 = clock64(); var += mp_t1 - mp_t0; mp_t0 = mp_t1; } while (0)
+#define MP_DECL(...) long long __VA_ARGS__
+#define MP_STORE(idx, v) g_mid_prof[blockIdx.x][idx] = (unsigned long long)(v)
+#else
+#define MP_T0()
+#define MP_ADD(var)
+#define MP_DECL(...)
+#define MP_STORE(idx, v)
+#endif
 
 template <bool RELU_IN>
 __global__ void __launch_bounds__(NUM_THREADS_MID, 1)
@@ -166,30 +202,40 @@ k_sepconv_mid(const __grid_constant__ CUtensorMap tmX /*3-D (C, W, B*H), box 64 
         if (lane == 0) {
             int xs = 0, bs = 0;
             uint32_t xph = 0, bph = 0;
+            MP_DECL(w_xe = 0, w_be = 0, w_iss = 0);
+            MP_T0();
             for (int item = blockIdx.x; item < g.items; item += gridDim.x) {
                 const int tile = item / g.n_halves, half = item - tile * g.n_halves;
                 const int r_lo = (tile * BM) / g.W;        // first global image row (b*H + y) the tile touches
                 const int n0 = half * NHALF;
                 for (int kc = 0; kc < g.kchunks; ++kc) {
+                    MP_ADD(w_iss);
                     mbar_wait(x_empty(xs), xph ^ 1u);
+                    MP_ADD(w_xe);
                     mbar_expect_tx(x_full(xs), g.x_bytes + DWW_BYTES);
                     const uint32_t xd = x_base + xs * XSTAGE;
                     tma_load_3d(xd, &tmX, x_full(xs), kc * CB, -1, r_lo - 1);
                     dwt::bulk_load_1d(xd + g.x_bytes, dwpad + (size_t)kc * 9 * CB, DWW_BYTES, x_full(xs));
                     if (++xs == NX) { xs = 0; xph ^= 1u; }
+                    MP_ADD(w_iss);
                     mbar_wait(b_empty(bs), bph ^ 1u);
+                    MP_ADD(w_be);
                     mbar_expect_tx(b_full(bs), B_BYTES);
                     tma_load_2d(b_base + bs * B_BYTES, &tmB, b_full(bs), kc * CB, n0);
                     tma_load_2d(b_base + bs * B_BYTES + NSUB * 128, &tmB, b_full(bs), kc * CB, n0 + NSUB);
                     if (++bs == NB) { bs = 0; bph ^= 1u; }
                 }
             }
+            MP_ADD(w_iss);
+            MP_STORE(0, w_xe); MP_STORE(1, w_be); MP_STORE(2, w_iss);
         }
     } else if (warp == 1) {
         // ================= MMA issuer =================
         if (lane == 0) {
             int as = 0, bs = 0, it = 0;
             uint32_t aph = 0, bph = 0;
+            MP_DECL(w_te = 0, w_af = 0, w_bf = 0, w_iss = 0);
+            MP_T0();
             for (int item = blockIdx.x; item < g.items; item += gridDim.x, ++it) {
                 const int tile = item / g.n_halves, half = item - tile * g.n_halves;
                 const int n_valid = min(NHALF, g.N - half * NHALF);
@@ -197,11 +243,16 @@ k_sepconv_mid(const __grid_constant__ CUtensorMap tmX /*3-D (C, W, B*H), box 64 
                 const int n_second = n_valid > NSUB ? ((n_valid - NSUB + 15) & ~15) : 0;
                 const uint32_t idesc0 = make_idesc(BM, (uint32_t)n_first);
                 const uint32_t idesc1 = make_idesc(BM, (uint32_t)(n_second ? n_second : 16));
+                MP_ADD(w_iss);
                 mbar_wait(tempty_bar, (uint32_t)(it & 1) ^ 1u);   // the epilogue has drained the (single) accumulator
+                MP_ADD(w_te);
                 tc_fence_after();
                 for (int kc = 0; kc < g.kchunks; ++kc) {
+                    MP_ADD(w_iss);
                     mbar_wait(a_full(as), aph);
+                    MP_ADD(w_af);
                     mbar_wait(b_full(bs), bph);
+                    MP_ADD(w_bf);
                     tc_fence_after();
                     const uint64_t adesc = make_smem_desc<128>(a_base + as * A_BYTES);
                     const uint64_t bdesc0 = make_smem_desc<128>(b_base + bs * B_BYTES);
@@ -219,6 +270,8 @@ k_sepconv_mid(const __grid_constant__ CUtensorMap tmX /*3-D (C, W, B*H), box 64 
                 }
                 umma_commit(tfull_bar);
             }
+            MP_ADD(w_iss);
+            MP_STORE(3, w_te); MP_STORE(4, w_af); MP_STORE(5, w_bf); MP_STORE(6, w_iss);
         }
     } else if (warp < 6) {
         // ================= epilogue (warps 2..5): gemm_tc.cuh's standard path on a 128 x 384 tile =================
@@ -227,6 +280,8 @@ k_sepconv_mid(const __grid_constant__ CUtensorMap tmX /*3-D (C, W, B*H), box 64 
         const bool has_res = residual != nullptr;
         uint32_t chunk_no = 0;
         int it = 0;
+        MP_DECL(w_tf = 0, w_epi = 0);
+        MP_T0();
         for (int item = blockIdx.x; item < g.items; item += gridDim.x, ++it) {
             const int tile = item / g.n_halves, half = item - tile * g.n_halves;
             const int m0 = tile * BM, n0 = half * NHALF;
@@ -243,7 +298,9 @@ k_sepconv_mid(const __grid_constant__ CUtensorMap tmX /*3-D (C, W, B*H), box 64 
                                                               : make_uint4(0, 0, 0, 0);
             };
             if (has_res) load_res(0);
+            MP_ADD(w_epi);
             mbar_wait(tfull_bar, (uint32_t)(it & 1));
+            MP_ADD(w_tf);
             tc_fence_after();
 #pragma unroll
             for (int c = 0; c < NHALF / 64; ++c) {
@@ -286,6 +343,8 @@ k_sepconv_mid(const __grid_constant__ CUtensorMap tmX /*3-D (C, W, B*H), box 64 
             if (lane == 0) mbar_arrive(tempty_bar);
         }
         if (lane == 0) bulk_wait_all<0>();
+        MP_ADD(w_epi);
+        if (warp == 2 && lane == 0) { MP_STORE(7, w_tf); MP_STORE(8, w_epi); }
     } else {
         // ================= depthwise producers (warps 6..15) =================
         const int dt = threadIdx.x - 6 * 32;      // 0 .. 32*DW_WARPS-1
@@ -297,6 +356,8 @@ k_sepconv_mid(const __grid_constant__ CUtensorMap tmX /*3-D (C, W, B*H), box 64 
         const bool has_col1 = 2 * cp + 1 < g.W;
         int xs = 0, as = 0;
         uint32_t xph = 0, aph = 0;
+        MP_DECL(w_xf = 0, w_ae = 0, w_cmp = 0);
+        MP_T0();
         for (int item = blockIdx.x; item < g.items; item += gridDim.x) {
             const int tile = item / g.n_halves;
             const int g0 = tile * BM;
@@ -307,8 +368,11 @@ k_sepconv_mid(const __grid_constant__ CUtensorMap tmX /*3-D (C, W, B*H), box 64 
             const int y_hi = min(y_lo + g.RS, nr);
             const int yimg_lo = (r_lo + y_lo) % g.H;           // position of the strip's first output row inside its image
             for (int kc = 0; kc < g.kchunks; ++kc) {
+                MP_ADD(w_cmp);
                 mbar_wait(x_full(xs), xph);
+                MP_ADD(w_xf);
                 mbar_wait(a_empty(as), aph ^ 1u);
+                MP_ADD(w_ae);
                 if (active && y_lo < y_hi) {
                     const uint32_t xt = x_base + xs * XSTAGE;
                     const uint32_t wb = xt + g.x_bytes + (uint32_t)cg * 16u;
@@ -350,26 +414,53 @@ k_sepconv_mid(const __grid_constant__ CUtensorMap tmX /*3-D (C, W, B*H), box 64 
                         }
                     };
                     // yi = position inside its image of the INPUT row being scattered; a row contributes upwards (bottom taps of the
-                    // output row above) only if it is not the first row of its image, downwards only if it is not the last.
+                    // output row above) only if it is not the first row of its image, downwards only if it is not the last.  The
+                    // rows next to an image boundary take a specialised copy of the scatter (warp-uniform branch), all others the
+                    // full one; the next row's pixels are always in flight while the current row is processed.
                     int yi = yimg_lo == 0 ? g.H - 1 : yimg_lo - 1;
+                    const int last = g.H - 1;
+                    dwt::Px in[4];
+                    Raw cur = load_raw(rowaddr);
+                    Raw nxt = load_raw(rowaddr + rowpitch);
+                    rowaddr += 2u * rowpitch;
                     // input row y_lo - 1: only its top taps matter (they open output row y_lo)
-                    scatter_row_masked<RELU_IN>(rowaddr, wl, wh, aA, aB, aC, false, false, yi != g.H - 1);
+                    unpack_raw<RELU_IN>(cur, in);
+                    if (yi != last) scatter_px<false, false, true>(in, wl, wh, aA, aB, aC);
+                    else scatter_px<false, false, false>(in, wl, wh, aA, aB, aC);
                     rotate();
-                    rowaddr += rowpitch;
                     if (++yi == g.H) yi = 0;
+                    cur = nxt;
+                    nxt = load_raw(rowaddr);
+                    rowaddr += rowpitch;
                     // input row y_lo: middle taps of row y_lo, top taps of row y_lo + 1
-                    scatter_row_masked<RELU_IN>(rowaddr, wl, wh, aA, aB, aC, false, true, yi != g.H - 1);
+                    unpack_raw<RELU_IN>(cur, in);
+                    if (yi != last) scatter_px<false, true, true>(in, wl, wh, aA, aB, aC);
+                    else scatter_px<false, true, false>(in, wl, wh, aA, aB, aC);
                     rotate();
-                    rowaddr += rowpitch;
                     if (++yi == g.H) yi = 0;
+                    cur = nxt;
                     for (int r = y_lo + 1; r < y_hi; ++r, rowaddr += rowpitch) {
-                        scatter_row_masked<RELU_IN>(rowaddr, wl, wh, aA, aB, aC, yi != 0, true, yi != g.H - 1);
+                        nxt = load_raw(rowaddr);
+                        unpack_raw<RELU_IN>(cur, in);
+                        if (yi == 0) scatter_px<false, true, true>(in, wl, wh, aA, aB, aC);
+                        else if (yi == last) scatter_px<true, true, false>(in, wl, wh, aA, aB, aC);
+                        else scatter_px<true, true, true>(in, wl, wh, aA, aB, aC);
                         store_row();
                         rotate();
                         if (++yi == g.H) yi = 0;
+                        cur = nxt;
                     }
                     // input row y_hi: only its bottom taps matter (they close output row y_hi - 1)
-                    scatter_row_masked<RELU_IN>(rowaddr, wl, wh, aA, aB, aC, yi != 0, false, false);
+                    unpack_raw<RELU_IN>(cur, in);
+                    if (yi != 0) {
+#pragma unroll
+                        for (int j = 0; j < 2; ++j)
+#pragma unroll
+                            for (int kx = 0; kx < 3; ++kx) {
+                                aA[j][0] = ffma2(in[j + kx].lo, wl[6 + kx], aA[j][0]);
+                                aA[j][1] = ffma2(in[j + kx].hi, wh[6 + kx], aA[j][1]);
+                            }
+                    }
                     store_row();
                 }
                 fence_proxy_async_smem();  // make the generic-proxy A-tile stores visible to the tensor core (async proxy)
@@ -381,6 +472,11 @@ k_sepconv_mid(const __grid_constant__ CUtensorMap tmX /*3-D (C, W, B*H), box 64 
                 if (++xs == NX) { xs = 0; xph ^= 1u; }
                 if (++as == NA) { as = 0; aph ^= 1u; }
             }
+        }
+        MP_ADD(w_cmp);
+        if (lane == 0 && (warp == 6 || warp == 15)) {
+            const int o = warp == 6 ? 9 : 12;
+            MP_STORE(o, w_xf); MP_STORE(o + 1, w_ae); MP_STORE(o + 2, w_cmp);
         }
     }
     tc_fence_before();
