@@ -7,7 +7,7 @@ Asserted (and written to gpurun_out/accuracy512.json for BASELINE.md):
   * calibrated_mild, natural head: the north_star contract -- EVERY one of the 512 pictures within 2e-2; top-1 identical on every
     picture whose fp64 top-2 margin is larger than the error the contract allows (2 x 2e-2 x max|logit|), >= 99.5 % overall (a
     picture whose two best classes are tied to within the tolerance can legitimately land on either side);
-  * calibrated (hostile init), natural head: mean <= 2e-2, p95 <= 2.5e-2, max <= 3.5e-2, top-1 as above with >= 97 % overall --
+  * calibrated (hostile init), natural head: mean <= 2e-2, p95 <= 2.5e-2, max <= 3.5e-2, top-1 as above with >= 95 % overall --
     the accepted deviation (oracle/bf16_model.py predicts mean 1.1e-2 / p95 1.7e-2 / max 2.6e-2 from bf16 rounding alone);
   * both inits, head re-centred on the 512 feature vectors (>= 6 argmax classes): top-1 agreement on every picture whose fp64
     margin exceeds the error bound, >= 99 % overall, and the image-dependent error <= 2e-2 (mild) / 3e-2 (hostile) of the
@@ -72,7 +72,7 @@ def test_bf16_accuracy_over_512_structured_pictures(golden_dir, init):
     else:
         assert errs.mean() <= BF16_TOL and np.percentile(errs, 95) <= 2.5e-2 and errs.max() <= 3.5e-2, rep
     assert agree[decided_nat].all() and decided_nat.sum() >= n // 2, rep
-    assert agree.mean() >= (0.97 if hostile else 0.995), rep
+    assert agree.mean() >= (0.95 if hostile else 0.995), rep
     assert sig.max() <= (1.5 * BF16_TOL if hostile else BF16_TOL), rep
     assert agree_c[decided].all(), rep
     assert agree_c.mean() >= 0.99, rep
