@@ -336,7 +336,7 @@ template <typename T> struct Runner {
                   "sepfused H=%d K=%d N=%d", H, g.K, g.N);
         no_flip();
         int rc = sepc::launch(m->tma, (const bf16 *)in, m->dwpad[si], &g.tmB, g.bias, (bf16 *)out, B, H, H, g.K, g.N, ld(g.K), ld(g.N),
-                              relu_in, relu_out, st, m->err);
+                              relu_in, relu_out, st, m->err, si);
         prof_close(m, st);
         if (rc != KDL_OK) return rc;
         m->launches++;
@@ -1227,5 +1227,9 @@ extern "C" int kdl_profile_end(KdlModel *m, KdlProfileRow *rows, int32_t capacit
 // probe builds only (make prof): cycle counters of the last k_sepconv_mid launch, [ctas][32]
 extern "C" int kdl_mid_prof_read(unsigned long long *out, int ctas) {
     return cudaMemcpyFromSymbol(out, kdl::sepm::g_mid_prof, sizeof(unsigned long long) * 32 * (size_t)ctas) == cudaSuccess ? 0 : -2;
+}
+// [4 launches][160 CTAs][16 counters] of the k_sepconv_tc launches of the last forward (slot = sepconv index 0..3)
+extern "C" int kdl_sep_prof_read(unsigned long long *out) {
+    return cudaMemcpyFromSymbol(out, kdl::sepc::g_sep_prof, sizeof(unsigned long long) * 4 * 160 * 16) == cudaSuccess ? 0 : -2;
 }
 #endif

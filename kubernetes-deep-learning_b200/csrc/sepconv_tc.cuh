@@ -44,7 +44,22 @@ struct Geom {
     int B, H, W, K, N;       // spatial size (stride 1, SAME), channels in / out
     int ntx, nty, num_tiles, kchunks;
     int relu_out;
+    int prof_slot;           // probe builds (-DKDL_MID_PROF): which row block of g_sep_prof this launch writes
 };
+
+// -DKDL_MID_PROF (probe builds only): per-role wait / work cycle counters, [launch slot][CTA][counter]
+#ifdef KDL_MID_PROF
+__device__ unsigned long long g_sep_prof[4][160][16];
+#define SP_T0() long long sp_t0 = clock64()
+#define SP_ADD(var) do { long long sp_t1 = clock64(); var += sp_t1 - sp_t0; sp_t0 = sp_t1; } while (0)
+#define SP_DECL(...) long long __VA_ARGS__
+#define SP_STORE(idx, v) g_sep_prof[g.prof_slot & 3][blockIdx.x][idx] = (unsigned long long)(v)
+#else
+#define SP_T0()
+#define SP_ADD(var)
+#define SP_DECL(...)
+#define SP_STORE(idx, v)
+#endif
 
 __device__ __forceinline__ void tma_store_4d(const CUtensorMap *tm, uint32_t src, int c0, int c1, int c2, int c3) {
     asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(tm), "r"(src), "r"(c0),
@@ -108,23 +123,31 @@ k_sepconv_tc(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
         if (lane == 0) {
             int xs = 0, bs = 0;
             uint32_t xph = 0, bph = 0;
+            SP_DECL(w_xe = 0, w_be = 0, w_i = 0);
+            SP_T0();
             for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x) {
                 const int tx = tile % g.ntx;
                 const int r = tile / g.ntx;
                 const int ty = r % g.nty, b = r / g.nty;
                 for (int kc = 0; kc < g.kchunks; ++kc) {
+                    SP_ADD(w_i);
                     mbar_wait(x_empty(xs), xph ^ 1u);
+                    SP_ADD(w_xe);
                     mbar_expect_tx(x_full(xs), XSTAGE);
                     const uint32_t xd = x_base + xs * XSTAGE;
                     dwt::tma_load_4d(xd, &tmX, x_full(xs), kc * CB, tx * TW - 1, ty * TH - 1, b);
                     dwt::bulk_load_1d(xd + X_BYTES, dwpad + (size_t)kc * 9 * CB, DWW_BYTES, x_full(xs));
                     if (++xs == NX) { xs = 0; xph ^= 1u; }
+                    SP_ADD(w_i);
                     mbar_wait(b_empty(bs), bph ^ 1u);
+                    SP_ADD(w_be);
                     mbar_expect_tx(b_full(bs), B_BYTES);
                     tma_load_2d(b_base + bs * B_BYTES, &tmB, b_full(bs), kc * CB, 0);
                     if (++bs == NB) { bs = 0; bph ^= 1u; }
                 }
             }
+            SP_ADD(w_i);
+            SP_STORE(0, w_xe); SP_STORE(1, w_be); SP_STORE(2, w_i);
         }
     } else if (warp == 1) {
         // ================= MMA issuer =================
@@ -132,14 +155,21 @@ k_sepconv_tc(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
             int as = 0, bs = 0, it = 0;
             uint32_t aph = 0, bph = 0;
             const uint32_t idesc = make_idesc(BLOCK_M, (uint32_t)((g.N + 15) & ~15));
+            SP_DECL(w_te = 0, w_af = 0, w_bf = 0, w_i = 0);
+            SP_T0();
             for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x, ++it) {
                 const int acc = it & 1;
+                SP_ADD(w_i);
                 mbar_wait(tempty_bar(acc), (uint32_t)((it >> 1) & 1) ^ 1u);
+                SP_ADD(w_te);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + acc * BN;
                 for (int kc = 0; kc < g.kchunks; ++kc) {
+                    SP_ADD(w_i);
                     mbar_wait(a_full(as), aph);
+                    SP_ADD(w_af);
                     mbar_wait(b_full(bs), bph);
+                    SP_ADD(w_bf);
                     tc_fence_after();
                     const uint64_t adesc = make_smem_desc<128>(a_base + as * A_BYTES);
                     const uint64_t bdesc = make_smem_desc<128>(b_base + bs * B_BYTES);
@@ -153,6 +183,8 @@ k_sepconv_tc(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
                 }
                 umma_commit(tfull_bar(acc));
             }
+            SP_ADD(w_i);
+            SP_STORE(3, w_te); SP_STORE(4, w_af); SP_STORE(5, w_bf); SP_STORE(6, w_i);
         }
     } else if (warp < 6) {
         // ================= epilogue (warps 2..5) =================
@@ -160,13 +192,17 @@ k_sepconv_tc(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
         const uint32_t ebuf = epi_base + (uint32_t)(warp - 2) * 8192u;
         uint32_t chunk_no = 0;
         int it = 0;
+        SP_DECL(w_tf = 0, w_w = 0);
+        SP_T0();
         for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x, ++it) {
             const int tx = tile % g.ntx;
             const int rr = tile / g.ntx;
             const int ty = rr % g.nty, b = rr / g.nty;
             const int acc = it & 1;
             const uint32_t t_row = tmem_base + acc * BN + ((uint32_t)(q * 32) << 16);
+            SP_ADD(w_w);
             mbar_wait(tfull_bar(acc), (uint32_t)((it >> 1) & 1));
+            SP_ADD(w_tf);
             tc_fence_after();
             // rows 32q..32q+31 of the tile = pixel rows (2q, 2q+1) x 16 columns; a warp whose rows lie below the image skips the
             // chunk entirely (no buffer write, no store) so that store groups and staging buffers stay in lock-step
@@ -200,6 +236,8 @@ k_sepconv_tc(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
             if (lane == 0) mbar_arrive(tempty_bar(acc));
         }
         if (lane == 0) bulk_wait_all<0>();
+        SP_ADD(w_w);
+        if (warp == 2 && lane == 0) { SP_STORE(7, w_tf); SP_STORE(8, w_w); }
     } else {
         // ================= depthwise producers (warps 6..13) =================
         const int dt = threadIdx.x - 6 * 32;      // 0..32*DW_WARPS-1
@@ -209,10 +247,15 @@ k_sepconv_tc(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
         const int y_hi = min(y_lo + DW_ROWS, TH);
         int xs = 0, as = 0;
         uint32_t xph = 0, aph = 0;
+        SP_DECL(w_xf = 0, w_ae = 0, w_c = 0);
+        SP_T0();
         for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x) {
             for (int kc = 0; kc < g.kchunks; ++kc) {
+                SP_ADD(w_c);
                 mbar_wait(x_full(xs), xph);
+                SP_ADD(w_xf);
                 mbar_wait(a_empty(as), aph ^ 1u);
+                SP_ADD(w_ae);
                 const uint32_t xt = x_base + xs * XSTAGE;
                 const uint32_t wb = xt + X_BYTES + (uint32_t)cg * 16u;
                 float2 wl[9], wh[9];
@@ -269,6 +312,8 @@ k_sepconv_tc(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
                 if (++as == NA) { as = 0; aph ^= 1u; }
             }
         }
+        SP_ADD(w_c);
+        if (warp == 6 && lane == 0) { SP_STORE(9, w_xf); SP_STORE(10, w_ae); SP_STORE(11, w_c); }
     }
     tc_fence_before();
     __syncthreads();
@@ -293,8 +338,9 @@ inline bool supported(int K, int N) { return K >= 64 && K <= 256 && (K % 64) == 
 
 // in [B,H,W,K] (pitch ld_in), dwpad [K/64][9][64] fp32, pointwise weights via tmB (box 64 x 256 over Wt[N][Kp]), out [B,H,W,N] (pitch ld_out)
 inline int launch(const TmaEncoder &enc, const bf16 *in, const float *dwpad, const CUtensorMap *tmB, const float *bias, bf16 *out, int B,
-                  int H, int W, int K, int N, int ld_in, int ld_out, int relu_in, int relu_out, cudaStream_t st, char *err) {
+                  int H, int W, int K, int N, int ld_in, int ld_out, int relu_in, int relu_out, cudaStream_t st, char *err, int prof_slot = 0) {
     Geom g;
+    g.prof_slot = prof_slot;
     g.B = B; g.H = H; g.W = W; g.K = K; g.N = N;
     g.ntx = (W + TW - 1) / TW;
     g.nty = (H + TH - 1) / TH;
