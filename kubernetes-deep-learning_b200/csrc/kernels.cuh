@@ -68,11 +68,33 @@ k_resize(const uint8_t *__restrict__ src, const ImgMeta *__restrict__ meta, cons
     const ImgMeta mt = meta[b];
     const uint8_t *srow = src + mt.offset + (long long)ytab[(size_t)b * S + y] * mt.pitch;
     const int32_t *xt = xtab + (size_t)b * S;
-    for (int x = threadIdx.x; x < S; x += blockDim.x) {
-        const uint8_t *p = srow + (long long)xt[x] * 3;
-        rowbuf[3 * x + 0] = __ldg(p);
-        rowbuf[3 * x + 1] = __ldg(p + 1);
-        rowbuf[3 * x + 2] = __ldg(p + 2);
+    // Source bytes are fetched as ALIGNED 32-bit words and funnel-shifted into place (an aligned word that holds a wanted byte can
+    // never leave the allocation or the page): a pixel costs one or two word loads instead of three byte loads, and when the
+    // source row already has the target width (identity x-table) the row is streamed word by word, fully coalesced.
+    if (mt.w == S) {
+        const uintptr_t a0 = reinterpret_cast<uintptr_t>(srow);
+        const uint32_t *wbase = reinterpret_cast<const uint32_t *>(a0 & ~uintptr_t(3));
+        const int k0 = (int)(a0 & 3);
+        const unsigned sh = (unsigned)k0 * 8u;
+        uint32_t *rb = reinterpret_cast<uint32_t *>(rowbuf);
+        const int nwords = (n + 3) >> 2;                        // the last word may carry up to 3 bytes past the row: rowbuf has room
+        for (int i = threadIdx.x; i < nwords; i += blockDim.x) {
+            const uint32_t lo = __ldg(wbase + i);
+            const uint32_t hi = (k0 != 0 && 4 * i + 4 < n + k0) ? __ldg(wbase + i + 1) : 0u;   // only if it still holds row bytes
+            rb[i] = __funnelshift_r(lo, hi, sh);
+        }
+    } else {
+        for (int x = threadIdx.x; x < S; x += blockDim.x) {
+            const uintptr_t a = reinterpret_cast<uintptr_t>(srow) + (uintptr_t)xt[x] * 3u;
+            const uint32_t *wp = reinterpret_cast<const uint32_t *>(a & ~uintptr_t(3));
+            const unsigned k = (unsigned)(a & 3);
+            const uint32_t lo = __ldg(wp);
+            const uint32_t hi = k > 1 ? __ldg(wp + 1) : 0u;     // bytes k..k+2 reach into the next word only for k = 2, 3
+            const uint32_t px = __funnelshift_r(lo, hi, k * 8u);
+            rowbuf[3 * x + 0] = (uint8_t)px;
+            rowbuf[3 * x + 1] = (uint8_t)(px >> 8);
+            rowbuf[3 * x + 2] = (uint8_t)(px >> 16);
+        }
     }
     __syncthreads();
     TOut *orow = out + ((size_t)b * S + y) * n;
