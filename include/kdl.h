@@ -54,7 +54,7 @@ typedef struct KdlConfig {
 /* Kernel-selection switches of one model (no reference counterpart: TF-Serving has no such knobs; these exist so that A/B
  * measurements and the bit-identity tests of tests/test_gpu_variants.py do not depend on hidden environment variables).
  * kdl_create installs the defaults; kdl_set_tuning takes effect from the next forward pass and drops the cached CUDA graphs.
- * All variants compute the same arithmetic in the same order: results are bit-identical whatever is selected. */
+ * Except where noted, variants compute the same arithmetic in the same order: results are bit-identical whatever is selected. */
 typedef struct KdlTuning {
     int32_t pdl_max_batch;       /* programmatic dependent launch for forwards of at most this many images (default 64; 0 = never) */
     int32_t serpentine;          /* !=0 (default): kernels walk their tiles in alternating directions so a consumer starts on the
@@ -64,7 +64,11 @@ typedef struct KdlTuning {
     int32_t fused_midflow;       /* !=0: 728 -> 728 layers at 19 x 19 (middle flow, block13_sepconv1) run the fused depthwise+pointwise
                                     kernel with flat-pixel tiles (sepconv_mid.cuh).  Default 0: it is bit-identical but measured
                                     slower than k_dw_tma + k_gemm_tc on a B200 (DESIGN.md §4 has the cycle breakdown) */
-    int32_t reserved[7];         /* must be 0 */
+    int32_t conv1_tc;            /* !=0 (default): block1_conv1 of the uint8 path runs as a tcgen05 implicit GEMM on the raw pixel
+                                    values (exact in bf16; x/127.5-1 folded into bf16 weights + fp32 bias).  0: the CUDA-core kernel
+                                    with fp32 weights (always used for float inputs and the fp32 path).  The ONE switch that
+                                    changes bits: conv1's weights are rounded to bf16 like every other layer's */
+    int32_t reserved[6];         /* must be 0 */
 } KdlTuning;
 int kdl_get_tuning(const KdlModel *m, KdlTuning *out);
 int kdl_set_tuning(KdlModel *m, const KdlTuning *t);

@@ -16,6 +16,7 @@
 #include "../../include/kdl.h"
 #include "gemm_tc.cuh"
 #include "conv_tc.cuh"
+#include "conv1_tc.cuh"
 #include "dw_tma.cuh"
 #include "pool_tma.cuh"
 #include "sepconv_tc.cuh"
@@ -108,6 +109,9 @@ struct KdlModel {
 
     // weights
     float *w_conv1 = nullptr, *b_conv1 = nullptr;
+    bf16 *w_conv1_tc = nullptr;       // [32 co][64 k] bf16: w_folded / 127.5, k >= 27 zero (tensor-core conv1 on raw uint8 pixels)
+    float *b_conv1_tc = nullptr;      // shift - sum_k w_folded
+    CUtensorMap tm_conv1;
     GemmW conv2, res[4];
     std::vector<float *> dw;      // [34] [9][C]
     std::vector<float *> dwpad;   // [34] [ceil(C/64)][9][64] zero padded (TMA depthwise kernel)
@@ -197,6 +201,7 @@ static KdlTuning default_tuning() {
     t.serpentine = 1;
     t.conv2_shifted_taps = 0;
     t.fused_sepconv = 1;
+    t.conv1_tc = 1;
     t.fused_midflow = 0;   // built, bit-identical, measured: 246 us per 728->728 layer at batch 256 against 165 us for k_dw_tma + k_gemm_tc
     return t;
 }
@@ -414,7 +419,10 @@ template <typename T> struct Runner {
             prof_open(m, st, PC_CONV1, 2.0 * 27 * 32 * B * sp[1] * sp[1],
                       (double)B * sp[0] * sp[0] * 3 * (in_f32 ? 4 : 1) + (double)B * sp[1] * sp[1] * 32 * sizeof(T));
             if (in_f32) launch_k(k_conv1<float, T>, dim3(grid), dim3(128), 0, st, in_f32, m->w_conv1, m->b_conv1, U, B, sp[0], sp[1]);
-            else launch_k(k_conv1<uint8_t, T>, dim3(grid), dim3(128), 0, st, in_u8, m->w_conv1, m->b_conv1, U, B, sp[0], sp[1]);
+            else if (use_tc() && m->tune.conv1_tc && m->w_conv1_tc) {   // raw uint8 pixels are exact in bf16: tensor-core implicit GEMM
+                int rc = c1tc::launch(in_u8, &m->tm_conv1, m->b_conv1_tc, (bf16 *)U, B, sp[0], sp[1], st, m->err);
+                if (rc != KDL_OK) return rc;
+            } else launch_k(k_conv1<uint8_t, T>, dim3(grid), dim3(128), 0, st, in_u8, m->w_conv1, m->b_conv1, U, B, sp[0], sp[1]);
             prof_close(m, st);
             LAUNCH_CHECK();
             RUN(tap("block1_conv1_act", U, sp[1], 32, 1));
@@ -636,6 +644,26 @@ extern "C" int kdl_load_weights(KdlModel *m, const float *blob, size_t n_floats)
         for (int i = 0; i < 27; ++i) for (int c = 0; c < 32; ++c) w[i * 32 + c] = k[i * 32 + c] * f.scale[c];
         if ((rc = upload(m, (void **)&m->w_conv1, w.data(), w.size() * 4))) return rc;
         if ((rc = upload(m, (void **)&m->b_conv1, f.shift.data(), 32 * 4))) return rc;
+        if (m->cfg.precision == KDL_PRECISION_BF16 && m->tma.ok()) {
+            // x = v/127.5 - 1 folded into the operands (conv1_tc.cuh): the MMA multiplies raw pixel values, exact in bf16
+            std::vector<uint16_t> wt(32 * 64, 0);
+            std::vector<float> bt(32);
+            for (int c = 0; c < 32; ++c) {
+                double sum = 0.0;
+                for (int i = 0; i < 27; ++i) {
+                    const double wf = (double)k[i * 32 + c] * (double)f.scale[c];
+                    sum += wf;
+                    wt[c * 64 + i] = f2bf((float)(wf / 127.5));
+                }
+                bt[c] = (float)((double)f.shift[c] - sum);
+            }
+            if ((rc = upload(m, (void **)&m->w_conv1_tc, wt.data(), wt.size() * 2))) return rc;
+            if ((rc = upload(m, (void **)&m->b_conv1_tc, bt.data(), 32 * 4))) return rc;
+            if (!m->tma.encode_2d(&m->tm_conv1, m->w_conv1_tc, 64, 32, 128, 64, 32, 128)) {
+                set_err(m->err, "cuTensorMapEncodeTiled failed for the conv1 weight tile");
+                return KDL_ECUDA;
+            }
+        }
     }
     {
         const float *k = p; p += 288 * 64;
@@ -782,7 +810,7 @@ extern "C" int kdl_create(const KdlConfig *cfg, KdlModel **out) {
     }
     CKM(cudaStreamCreateWithFlags(&m->own_stream, cudaStreamNonBlocking));
     m->tune = default_tuning();
-    if ((rc = tc::configure(m->err)) != KDL_OK || (rc = convtc::configure(m->err)) != KDL_OK || (rc = dwt::configure(m->err)) != KDL_OK || (rc = poolt::configure(m->err)) != KDL_OK || (rc = sepc::configure(m->err)) != KDL_OK || (rc = sepm::configure(m->err)) != KDL_OK) { set_err(g_err, "%s", m->err); kdl_destroy(m); return rc; }
+    if ((rc = tc::configure(m->err)) != KDL_OK || (rc = convtc::configure(m->err)) != KDL_OK || (rc = dwt::configure(m->err)) != KDL_OK || (rc = poolt::configure(m->err)) != KDL_OK || (rc = sepc::configure(m->err)) != KDL_OK || (rc = sepm::configure(m->err)) != KDL_OK || (rc = c1tc::configure(m->err)) != KDL_OK) { set_err(g_err, "%s", m->err); kdl_destroy(m); return rc; }
 #undef CKM
     *out = m;
     return KDL_OK;
@@ -835,7 +863,7 @@ extern "C" int kdl_set_tuning(KdlModel *m, const KdlTuning *t) {
 extern "C" const char *kdl_last_error(const KdlModel *m) { return m ? m->err : g_err; }
 extern "C" int kdl_last_launch_count(const KdlModel *m) { return m ? m->launches : 0; }
 extern "C" const char *kdl_version(void) {
-    return "kdl 0.3 sm_100a: k_resize k_conv1 k_conv3x3_tc k_dw_tma k_sepconv_tc k_sepconv_mid k_pool_tma k_gemm_tc(tcgen05/TMEM/TMA) k_gap_partial k_head_finish";
+    return "kdl 0.3 sm_100a: k_resize k_conv1 k_conv1_tc k_conv3x3_tc k_dw_tma k_sepconv_tc k_sepconv_mid k_pool_tma k_gemm_tc(tcgen05/TMEM/TMA) k_gap_partial k_head_finish";
 }
 
 // ---------------------------------------------------------------------------------------------------

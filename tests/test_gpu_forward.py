@@ -130,22 +130,55 @@ def test_bf16_path_logits_top1_and_layers(h, init, gemm):
 
 
 def test_fused_uint8_path_matches_two_step():
-    """predict_uint8 (resize+scale fused into the conv1 load) == preprocess then serving_default."""
+    """predict_uint8 (resize+scale fused into the conv1 load) == preprocess then serving_default: bit for bit when both run the
+    CUDA-core conv1 (fp32 path; bf16 path with KdlTuning.conv1_tc = 0).  With the tensor-core conv1 (the bf16 default for uint8
+    input: raw pixel values are exact in bf16, x/127.5-1 is folded into bf16 weights) only conv1's weight rounding differs."""
     from kdl_b200 import weights
+    from oracle import structured as S
     W = weights.make_weights(1, "calibrated")
-    rng = np.random.default_rng(11)
-    imgs = [rng.integers(0, 256, (int(rng.integers(64, 900)), int(rng.integers(64, 900)), 3), dtype=np.uint8)
-            for _ in range(5)]
-    for prec in ("f32", "bf16"):
-        m = _mk(W, max_batch=8, precision=prec)
+    imgs = S.structured_images(5)
+    for prec, tuning in (("f32", None), ("bf16", {"conv1_tc": 0}), ("bf16", None)):
+        m = _mk(W, max_batch=8, precision=prec, tuning=tuning)
         try:
             x = m.preprocess_uint8(imgs)
             two = m.forward_device(x).cpu().numpy()
             one = m.predict_uint8(imgs)
             assert one.shape == (5, 10)
-            np.testing.assert_array_equal(one, two)   # same arithmetic, same kernels after conv1's load
+            if prec == "f32" or tuning:
+                np.testing.assert_array_equal(one, two)   # same arithmetic, same kernels after conv1's load
+            else:
+                errs = [rel(one[i], two[i]) for i in range(5)]
+                assert 0 < max(errs) <= 1e-2, errs
         finally:
             m.close()
+
+
+def test_tensor_core_conv1_against_the_oracle():
+    """block1_conv1 as a tcgen05 implicit GEMM on raw uint8 pixels (conv1_tc.cuh), checked where it writes: the block1_conv1_act
+    tap of the uint8 path against the fp64 oracle on the Pillow-preprocessed pictures, mixed source sizes, two batch sizes (a
+    partial last tile and >1 tile per CTA), and against the CUDA-core conv1 (fp32 weights) on the same input."""
+    from kdl_b200 import weights
+    from oracle import preprocess_oracle as po
+    from oracle import structured as S
+    W = weights.make_weights(1, "calibrated")
+    for n, size in ((3, 299), (7, 150)):
+        imgs = S.structured_images(n)
+        x = np.concatenate([po.preprocess_pillow(im, size, size) for im in imgs])
+        taps = {}
+        _oracle(W, x[:2], taps)
+        want = np.maximum(taps["block1_conv1_act"], 0)
+        got = {}
+        for tc in (1, 0):
+            m = _mk(W, max_batch=8, input_size=size, precision="bf16", keep_taps=True, tuning={"conv1_tc": tc})
+            try:
+                m.predict_uint8(imgs)
+                got[tc], relu = m.layer_output("block1_conv1_act")
+                assert relu and got[tc].shape[0] == n
+            finally:
+                m.close()
+        assert rel(got[1][:2], want) <= 8e-3, rel(got[1][:2], want)        # bf16 output rounding (4e-3) + bf16 weights
+        assert rel(got[0][:2], want) <= 5e-3
+        assert rel(got[1], got[0]) <= 8e-3 and not np.array_equal(got[1], got[0])
 
 
 def test_batch_split_and_head_variant():
