@@ -28,7 +28,13 @@ constexpr uint32_t DWW_BYTES = 9 * CB * 4;
 constexpr uint32_t XSTAGE = X_BYTES + DWW_BYTES;
 constexpr uint32_t A_BYTES = 128 * 128;
 constexpr uint32_t B_BYTES = BN * 128;
-constexpr uint32_t EPI_BYTES = 4 * 2 * 4096;
+#ifndef KDL_SEP_EPI_WARPS
+#define KDL_SEP_EPI_WARPS 4
+#endif
+constexpr int EPI_WARPS = KDL_SEP_EPI_WARPS;          // 4, or 8 = two per TMEM lane quarter taking alternate 64-column chunks (needs NX = 2 to fit).
+                                                      // Measured equal (2.14 vs 2.16 ms): the role is not short of warps, it shares the FMA/ALU
+                                                      // pipes with the depthwise warps
+constexpr uint32_t EPI_BYTES = EPI_WARPS * 2 * 4096;
 constexpr uint32_t BIAS_BYTES = BN * 4;
 constexpr uint32_t SMEM_BYTES = NA * A_BYTES + NB * B_BYTES + EPI_BYTES + NX * XSTAGE + BIAS_BYTES + 256 + 1024;
 static_assert(SMEM_BYTES <= 232448, "exceeds 227 KB");
@@ -38,7 +44,8 @@ static_assert(XSTAGE % 128 == 0, "TMA destinations must stay 128-byte aligned");
 #endif
 constexpr int DW_WARPS = KDL_SEP_DW_WARPS;             // 8 = two 4-row strips, 12 = three strips (3,3,2 rows): more warps to hide LDS/FMA latency
 constexpr int DW_ROWS = DW_WARPS == 8 ? 4 : 3;
-constexpr int NUM_THREADS_SEP = (6 + DW_WARPS) * 32;
+constexpr int FIRST_DW_WARP = 2 + EPI_WARPS;
+constexpr int NUM_THREADS_SEP = (FIRST_DW_WARP + DW_WARPS) * 32;
 
 struct Geom {
     int B, H, W, K, N;       // spatial size (stride 1, SAME), channels in / out
@@ -99,13 +106,13 @@ k_sepconv_tc(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
         for (int s = 0; s < NX; ++s) { mbar_init(x_full(s), 1); mbar_init(x_empty(s), DW_WARPS); }
         for (int s = 0; s < NA; ++s) { mbar_init(a_full(s), DW_WARPS); mbar_init(a_empty(s), 1); }
         for (int s = 0; s < NB; ++s) { mbar_init(b_full(s), 1); mbar_init(b_empty(s), 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4); }
+        for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), EPI_WARPS); }
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(tmem_slot, 512);
-    if (warp >= 2 && warp < 6) {  // bias: one N tile for the whole kernel
+    if (warp >= 2 && warp < FIRST_DW_WARP) {  // bias: one N tile for the whole kernel
         const int et = threadIdx.x - 64;
-        for (int j = et; j < BN; j += 128) {
+        for (int j = et; j < BN; j += 32 * EPI_WARPS) {
             float b = j < g.N ? __ldg(bias + j) : 0.f;
             asm volatile("st.shared.f32 [%0], %1;" ::"r"(bias_base + 4u * j), "f"(b) : "memory");
         }
@@ -186,13 +193,16 @@ k_sepconv_tc(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
             SP_ADD(w_i);
             SP_STORE(3, w_te); SP_STORE(4, w_af); SP_STORE(5, w_bf); SP_STORE(6, w_i);
         }
-    } else if (warp < 6) {
-        // ================= epilogue (warps 2..5) =================
+    } else if (warp < FIRST_DW_WARP) {
+        // ================= epilogue (warps 2 .. FIRST_DW_WARP-1) =================
+        // In the write-heavy launches (64 -> 128 @147, 128 -> 256 @74) this role's ~120 instructions per 64-column chunk take ~2 k clk:
+        // its warps share the schedulers' FMA/ALU pipes with the depthwise warps, which have the higher warp ids and so the priority.
         const int q = warp & 3;
+        const int half = (warp - 2) >> 2;
         const uint32_t ebuf = epi_base + (uint32_t)(warp - 2) * 8192u;
         uint32_t chunk_no = 0;
         int it = 0;
-        SP_DECL(w_tf = 0, w_w = 0);
+        SP_DECL(w_tf = 0, w_w = 0, w_bw = 0, w_ld = 0, w_st = 0);
         SP_T0();
         for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x, ++it) {
             const int tx = tile % g.ntx;
@@ -210,25 +220,30 @@ k_sepconv_tc(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
 #pragma unroll
             for (int c = 0; c < BN / 64; ++c) {
                 const int nc = c * 64;
-                if (nc < g.N && do_store) {
+                if (nc < g.N && do_store && (c % (EPI_WARPS / 4)) == half) {
                     uint32_t r[64];
                     tmem_ld32(t_row + c * 64, r);
                     tmem_ld32(t_row + c * 64 + 32, r + 32);
                     const uint32_t buf = ebuf + (uint32_t)(chunk_no++ & 1u) * 4096u;
+                    SP_ADD(w_w);
                     if (lane == 0) bulk_wait_read<1>();
                     __syncwarp();
+                    SP_ADD(w_bw);
                     tmem_ld_wait();
+                    SP_ADD(w_ld);
 #pragma unroll
                     for (int gidx = 0; gidx < 8; ++gidx) {
                         const uint4 o = epi8(r + gidx * 8, bias_base + (uint32_t)(c * 64 + gidx * 8) * 4u, g.relu_out, false, make_uint4(0, 0, 0, 0));
                         st_shared_v4(buf + (uint32_t)lane * 128u + (uint32_t)((gidx ^ (lane & 7)) << 4), o);
                     }
+                    SP_ADD(w_w);
                     fence_proxy_async_smem();
                     __syncwarp();
                     if (lane == 0) {
                         tma_store_4d(&tmOut, buf, nc, tx * TW, ty * TH + 2 * q, b);
                         bulk_commit();
                     }
+                    SP_ADD(w_st);
                 }
             }
             tc_fence_before();
@@ -237,10 +252,10 @@ k_sepconv_tc(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
         }
         if (lane == 0) bulk_wait_all<0>();
         SP_ADD(w_w);
-        if (warp == 2 && lane == 0) { SP_STORE(7, w_tf); SP_STORE(8, w_w); }
+        if (warp == 2 && lane == 0) { SP_STORE(7, w_tf); SP_STORE(8, w_w); SP_STORE(12, w_bw); SP_STORE(13, w_ld); SP_STORE(14, w_st); }
     } else {
-        // ================= depthwise producers (warps 6..13) =================
-        const int dt = threadIdx.x - 6 * 32;      // 0..32*DW_WARPS-1
+        // ================= depthwise producers (warps FIRST_DW_WARP ..) =================
+        const int dt = threadIdx.x - FIRST_DW_WARP * 32;      // 0..32*DW_WARPS-1
         const int cg = dt & 15;                   // 4-channel group of the 64-channel chunk
         const int cp = (dt >> 4) & 7;             // column pair
         const int y_lo = (dt >> 7) * DW_ROWS;     // strip of output rows
@@ -313,7 +328,7 @@ k_sepconv_tc(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CU
             }
         }
         SP_ADD(w_c);
-        if (warp == 6 && lane == 0) { SP_STORE(9, w_xf); SP_STORE(10, w_ae); SP_STORE(11, w_c); }
+        if (warp == FIRST_DW_WARP && lane == 0) { SP_STORE(9, w_xf); SP_STORE(10, w_ae); SP_STORE(11, w_c); }
     }
     tc_fence_before();
     __syncthreads();

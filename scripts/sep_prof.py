@@ -21,7 +21,8 @@ lib.kdl_sep_prof_read.argtypes = [ctypes.c_void_p]
 assert lib.kdl_sep_prof_read(buf) == 0
 a = np.frombuffer(buf, dtype=np.uint64).reshape(4, 160, 16).astype(np.float64)[:, :148]
 names = ["prod wait x_empty", "prod wait b_empty", "prod issue", "mma wait tempty", "mma wait a_full", "mma wait b_full", "mma issue",
-         "epi wait tfull", "epi work", "dw wait x_full", "dw wait a_empty", "dw compute"]
+         "epi wait tfull", "epi math+sts", "dw wait x_full", "dw wait a_empty", "dw compute", "epi wait store-read", "epi wait tmem ld",
+         "epi fence+store issue"]
 layers = [("block2_sepconv1 64->128 @147", 147, 1), ("block2_sepconv2 128->128 @147", 147, 2), ("block3_sepconv1 128->256 @74", 74, 2),
           ("block3_sepconv2 256->256 @74", 74, 4)]
 for s, (nm, H, kch) in enumerate(layers):
