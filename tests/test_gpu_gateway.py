@@ -42,9 +42,13 @@ def test_apply_model_contract_on_fixture(gw, golden_dir):
     want = xo.forward(W, po.preprocess_pillow(src), torch.float64)[0]
     got = np.array(list(out.values()))
     assert rel(got, want) <= 2e-2 and got.argmax() == want.argmax()
+    # the in-process uint8 path (apply_model_array): same contract; it differs from the float-tensor path only by conv1's bf16
+    # weight rounding (raw pixels go to the tensor cores there, KdlTuning.conv1_tc)
     fused = g.apply_model_array(src)
     assert list(fused) == list(out)
-    np.testing.assert_array_equal(np.array(list(fused.values()), np.float32), got.astype(np.float32))
+    fv = np.array(list(fused.values()), np.float32)
+    assert rel(fv, want) <= 2e-2 and fv.argmax() == want.argmax()
+    assert rel(fv, got) <= 1e-2
 
 
 def test_unknown_model_or_signature_is_an_error(gw):
@@ -148,7 +152,8 @@ def test_unmodified_gateway_flow_over_grpc_and_http(gw, tmp_path):
             body = json.loads(r.read())
         assert list(body) == gateway.labels
         got = np.array(list(body.values()))
-        np.testing.assert_allclose(got, pred, rtol=0, atol=0)          # same engine, same logits as the gRPC path
+        assert rel(got, want) <= 2e-2 and got.argmax() == want.argmax()
+        assert rel(got, pred) <= 1e-2      # same engine; the uint8 route differs from the float-tensor (gRPC) route by conv1's weight rounding
     finally:
         srv.shutdown()
 
@@ -176,9 +181,9 @@ def test_batched_gateway_gives_each_concurrent_request_its_own_unbatched_answer(
             t.join(60)
         assert got == alone
         assert max(gb._u8_batcher.batch_sizes) > 1 and gb._u8_batcher.images_run == len(imgs)
-        # the float path (Predict) is coalesced too
+        # the float path (Predict) is coalesced too: identical to the same request sent through the unbatched gateway
         X = g.preprocessor.from_array(imgs[0])
         y = gb.Predict(gateway.make_request(X), timeout=20.0)
-        assert gateway.process_response(y) == alone[0]
+        assert gateway.process_response(y) == gateway.process_response(g.Predict(gateway.make_request(X), timeout=20.0))
     finally:
         gb.close()
