@@ -297,9 +297,11 @@ def main():
         lo, hi = replicas.shard_range(TOTAL, rank, world)
 
         def make_chunks(lo, hi):
+            # at least two chunks per rank, so that the H2D copy of one overlaps the kernels of the other (submit / wait pipeline)
+            step_ = min(B, max(64, -(-(hi - lo) // 2)))
             ch = []
-            for c0 in range(lo, hi, B):
-                n = min(B, hi - c0)
+            for c0 in range(lo, hi, step_):
+                n = min(step_, hi - c0)
                 ch.append((engine.PackedImages(synth_images(n, S, 5000 + c0), pinned=True),
                            torch.empty((n, 10), dtype=torch.float32).pin_memory()))
             return ch
