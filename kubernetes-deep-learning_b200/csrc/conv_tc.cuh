@@ -16,11 +16,12 @@ using namespace kdl::tc;
 
 constexpr int CIN = 32, COUT = 64;
 constexpr int ROWB = CIN * 2;                       // 64 bytes per activation row
-constexpr int STAGES = 5;
+constexpr int STAGES = 4;
 constexpr uint32_t MAX_STAGE_BYTES = 2 * 256 * ROWB;  // two TMA boxes of <= 256 rows
 constexpr uint32_t W_BYTES = 9 * COUT * ROWB;       // 36 KB
 constexpr uint32_t BIAS_BYTES = COUT * 4;
-constexpr uint32_t SMEM_BYTES = STAGES * MAX_STAGE_BYTES + W_BYTES + BIAS_BYTES + 256 + 1024;
+constexpr uint32_t EPI_BYTES = 4 * 2 * 4096;        // per epilogue warp: 2 x (32 rows x 128 B), linear (bulk-store source)
+constexpr uint32_t SMEM_BYTES = STAGES * MAX_STAGE_BYTES + W_BYTES + BIAS_BYTES + EPI_BYTES + 256 + 1024;
 static_assert(SMEM_BYTES <= 232448, "exceeds 227 KB");
 
 __global__ void __launch_bounds__(NUM_THREADS, 1)
@@ -32,7 +33,8 @@ k_conv3x3_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
     const uint32_t stage_bytes = 2u * (uint32_t)box_rows * ROWB;  // multiple of 128
     const uint32_t wres_base = smem_base + STAGES * MAX_STAGE_BYTES;
     const uint32_t bias_base = wres_base + W_BYTES;
-    const uint32_t bar_base = bias_base + BIAS_BYTES;
+    const uint32_t epi_base = bias_base + BIAS_BYTES;
+    const uint32_t bar_base = epi_base + EPI_BYTES;
     auto full_bar = [&](int s) { return bar_base + 8u * s; };
     auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
     auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
@@ -111,6 +113,8 @@ k_conv3x3_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         named_bar_sync(1, 128);
         int it = 0;
         const int hw = cg.Hin * cg.Win;
+        const uint32_t ebuf = epi_base + (uint32_t)(warp - 2) * 8192u;
+        uint32_t n_store = 0;
         for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
             const int acc = it & 1;
             const uint32_t acc_phase = (it >> 1) & 1;
@@ -128,20 +132,47 @@ k_conv3x3_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty_bar(acc));  // accumulator is in registers: release it before the stores
-            if (row < M && y < cg.Hout && x < cg.Wout) {
-                bf16 *o = out + ((size_t)(b * cg.Hout + y) * cg.Wout + x) * COUT;
-                // the next block's Conv2D(1x1, strides 2) reads only the even pixels: emit them compactly here instead of a separate pass
-                bf16 *os = (sub && !(y & 1) && !(x & 1))
-                               ? sub + ((size_t)(b * ((cg.Hout + 1) >> 1) + (y >> 1)) * ((cg.Wout + 1) >> 1) + (x >> 1)) * COUT
-                               : nullptr;
+            // Output rows go through shared memory and leave as bulk stores: a lane owns one pixel (128 contiguous bytes), so direct
+            // stores touched 32 cache lines per instruction with 16 bytes each (ncu round 1: L2 75 % busy).  The warp's 32 grid positions
+            // are consecutive, and so are their outputs except for the two skipped columns at the end of an image row: at most two
+            // contiguous runs [0, n1) and [s2, s2 + n2) of lanes, each one bulk store.
+            const bool valid = row < M && y < cg.Hout && x < cg.Wout;
+            const uint32_t buf = ebuf + (n_store++ & 1u) * 4096u;
+            if (lane == 0) bulk_wait_read<1>();   // one store group per tile: the group that read this buffer two tiles ago is done
+            __syncwarp();
+            bf16 *os = (sub && valid && !(y & 1) && !(x & 1))
+                           ? sub + ((size_t)(b * ((cg.Hout + 1) >> 1) + (y >> 1)) * ((cg.Wout + 1) >> 1) + (x >> 1)) * COUT
+                           : nullptr;
 #pragma unroll
-                for (int g = 0; g < 8; ++g) {
-                    const uint4 v = epi8(r + g * 8, bias_base + 32u * g, relu, false, make_uint4(0, 0, 0, 0));
-                    *reinterpret_cast<uint4 *>(o + g * 8) = v;
-                    if (os) *reinterpret_cast<uint4 *>(os + g * 8) = v;
+            for (int g = 0; g < 8; ++g) {
+                const uint4 v = epi8(r + g * 8, bias_base + 32u * g, relu, false, make_uint4(0, 0, 0, 0));
+                st_shared_v4(buf + (uint32_t)lane * 128u + 16u * g, v);
+                // the next block's Conv2D(1x1, strides 2) reads only the even pixels: emit them compactly here instead of a separate pass
+                if (os) *reinterpret_cast<uint4 *>(os + g * 8) = v;
+            }
+            fence_proxy_async_smem();
+            const unsigned vmask = __ballot_sync(0xffffffffu, valid);
+            if (lane == 0 && vmask) {
+                // runs of set bits in vmask (valid lanes); the output address of a run comes from its first lane's coordinates
+                unsigned m = vmask;
+                while (m) {
+                    const int s0 = __ffs(m) - 1;
+                    const unsigned from = m >> s0;
+                    const int n = (~from) ? __ffs(~from) - 1 : 32 - s0;
+                    const int rr0 = tile * BLOCK_M + q * 32 + s0;
+                    const int b0 = rr0 / hw;
+                    const int rem0 = rr0 - b0 * hw;
+                    const int y0 = rem0 / cg.Win, x0 = rem0 - y0 * cg.Win;
+                    bf16 *o = out + ((size_t)(b0 * cg.Hout + y0) * cg.Wout + x0) * COUT;
+                    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(o), "r"(buf + (uint32_t)s0 * 128u),
+                                 "r"((uint32_t)n * 128u)
+                                 : "memory");
+                    m = (s0 + n >= 32) ? 0u : (m & ~((1u << (s0 + n)) - 1u));
                 }
+                bulk_commit();
             }
         }
+        if (lane == 0) bulk_wait_all<0>();
     }
     tc_fence_before();
     __syncthreads();
