@@ -36,7 +36,9 @@ constexpr int BLOCK_K = 64;   // standard configuration: 64 bf16 = 128 bytes = o
 // NST = operand ring depth, EB = output staging buffers per epilogue warp.  Tensor-bound layers want a deep operand ring
 // (4 x 48 KB) and get by with 2 store buffers; the HBM-bound K<=256 layers are limited by TMA stores in flight, so they trade
 // one ring stage for 4 store buffers per warp.
-template <int SW, int BN, bool CONV, int NST = (CONV ? 12 : 4), int EB = 2> struct Cfg {
+// EW = epilogue warps: 4 (one per TMEM lane quarter), or 8 = two per quarter taking alternate 64-column chunks.  The K <= 256 layers
+// spend 16 MMAs per tile in the main loop and ~4 dependent epilogue chunks per warp: there the four warps are the bottleneck.
+template <int SW, int BN, bool CONV, int NST = (CONV ? 12 : 4), int EB = 2, int EW = 4> struct Cfg {
     static constexpr int BLOCK_N = BN;
     static constexpr int BLOCK_K = SW / 2;  // elements per k-block = one swizzle row
     static constexpr int STAGES = NST;
@@ -45,7 +47,9 @@ template <int SW, int BN, bool CONV, int NST = (CONV ? 12 : 4), int EB = 2> stru
     static constexpr uint32_t B_BYTES = CONV ? 0 : BN * SW;           // conv mode keeps all 9 weight taps resident instead
     static constexpr uint32_t W_RES_BYTES = CONV ? 9 * BN * SW : 0;   // 9 taps x [64 out-ch x 32 in-ch] bf16 = 36 KB
     static constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr uint32_t EPI_BYTES = CONV ? 0 : 4 * EB * 4096;  // per epilogue warp: EB x (32 rows x 128 B)
+    static constexpr int EPI_WARPS = EW;
+    static constexpr int THREADS = (2 + EW) * 32;
+    static constexpr uint32_t EPI_BYTES = CONV ? 0 : EW * EB * 4096;  // per epilogue warp: EB x (32 rows x 128 B)
     static constexpr uint32_t BIAS_BYTES = BN * 4;
     static constexpr uint32_t BAR_BYTES = 256;
     static constexpr uint32_t SMEM_BYTES = STAGES * STAGE_BYTES + W_RES_BYTES + EPI_BYTES + BIAS_BYTES + BAR_BYTES + 1024 /*align slack*/;
@@ -53,8 +57,11 @@ template <int SW, int BN, bool CONV, int NST = (CONV ? 12 : 4), int EB = 2> stru
     static_assert(SMEM_BYTES <= 232448, "exceeds 227 KB of shared memory per CTA");
     static_assert(2 * BN <= 512, "two accumulators must fit the 512 TMEM columns");
 };
-typedef Cfg<128, 256, false> CfgStd;
-typedef Cfg<128, 256, false, 3, 4> CfgHbm;
+#ifndef KDL_GEMM_STD_EW
+#define KDL_GEMM_STD_EW 4   /* 8 (one staging buffer per warp) measured slower on the K >= 728 layers: 3.49 vs 3.38 ms */
+#endif
+typedef Cfg<128, 256, false, 4, (KDL_GEMM_STD_EW == 8 ? 1 : 2), KDL_GEMM_STD_EW> CfgStd;
+typedef Cfg<128, 256, false, 3, 2, 8> CfgHbm;
 typedef Cfg<128, 64, false, 4, 2> CfgSmallM;   // 128 x 64 tiles: 4x more CTAs and half the operand bytes per CTA when M is small (latency)
 typedef Cfg<64, 64, true> CfgConv;
 
@@ -279,13 +286,13 @@ __device__ __forceinline__ uint4 epi8(const uint32_t *acc, uint32_t bias_addr, i
 // ---------------------------------------------------------------------------------------------------
 // the kernel
 // ---------------------------------------------------------------------------------------------------
-template <int SW, int BN, bool CONV, int NST = (CONV ? 12 : 4), int EB = 2>
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+template <int SW, int BN, bool CONV, int NST = (CONV ? 12 : 4), int EB = 2, int EW = 4>
+__global__ void __launch_bounds__((2 + EW) * 32, 1)
 k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
           const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes /*residual, box 64 x 128; L2 prefetch only*/,
           const float *__restrict__ bias, const bf16 *residual, bf16 *out, int M, int N, int K, int relu, ConvGeom cg,
           int ldo /*row pitch of out / residual in elements*/, int rev = 0 /*1: walk the tiles from the last to the first*/) {
-    typedef Cfg<SW, BN, CONV, NST, EB> C;
+    typedef Cfg<SW, BN, CONV, NST, EB, EW> C;
     constexpr int STAGES = C::STAGES;
     constexpr int BK = C::BLOCK_K;
     extern __shared__ uint8_t smem_raw[];
@@ -314,7 +321,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         prefetch_tmap(&tmB);
         if (!CONV) prefetch_tmap(&tmOut);
         for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), 4); }
+        for (int a = 0; a < 2; ++a) { mbar_init(tfull_bar(a), 1); mbar_init(tempty_bar(a), EW); }
         mbar_init(wres_bar, 1);
         fence_barrier_init();
     }
@@ -398,9 +405,11 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             }
         }
     } else {
-        // ================= epilogue: warps 2..5; TMEM lane quarter = warp % 4 =================
+        // ================= epilogue: warps 2..(1+EW); TMEM lane quarter = warp % 4; with EW = 8 warp pairs split the chunks =================
         const int q = warp & 3;
-        const int et = threadIdx.x - 64;  // 0..127
+        const int half = (warp - 2) >> 2;            // 0 for EW = 4
+        constexpr int CSTEP = EW / 4;                // chunk stride of a warp
+        const int et = threadIdx.x - 64;  // 0..32*EW-1
         const uint32_t ebuf = epi_base + (uint32_t)(warp - 2) * (uint32_t)(C::EPI_BUFS * 4096);
         const bool has_res = residual != nullptr;
         int staged_n0 = -1, pref_n0 = -1;
@@ -415,7 +424,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             // stage this tile's bias slice (all four epilogue warps share it); skipped while the N tile does not change, and the
             // values were prefetched into registers during the previous tile so no global-load latency sits between the barriers
             if (n0 != staged_n0) {
-                named_bar_sync(1, 128);
+                named_bar_sync(1, 32 * EW);
                 if (n0 != pref_n0) {
 #pragma unroll
                     for (int j = 0; j < (BN + 127) / 128; ++j)
@@ -424,7 +433,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
 #pragma unroll
                 for (int j = 0; j < (BN + 127) / 128; ++j)
                     if (et + 128 * j < BN) asm volatile("st.shared.f32 [%0], %1;" ::"r"(bias_base + 4u * (et + 128 * j)), "f"(bpre[j]) : "memory");
-                named_bar_sync(1, 128);
+                named_bar_sync(1, 32 * EW);
                 staged_n0 = n0;
             }
             {
@@ -477,7 +486,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
                         rn[g] = (rl_row + 4 * g < M && n < N) ? *reinterpret_cast<const uint4 *>(res_lane + (size_t)(4 * g) * ldo + n0 + c * 64)
                                                              : make_uint4(0, 0, 0, 0);
                 };
-                if (has_res) load_res(0);
+                if (has_res) load_res(half);
                 mbar_wait(tfull_bar(acc), acc_phase);
                 tc_fence_after();
 #ifndef KDL_ABLATE_EPI
@@ -486,7 +495,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
 #pragma unroll
                 for (int c = 0; c < BN / 64; ++c) {
                     const int nc = n0 + c * 64;
-                    if (nc < N && KDL_ABLATE_EPI != 1) {  // warp-uniform
+                    if (nc < N && KDL_ABLATE_EPI != 1 && (c % CSTEP) == half) {  // warp-uniform
                         uint32_t r[64];
                         tmem_ld32(t_row + c * 64, r);
                         tmem_ld32(t_row + c * 64 + 32, r + 32);
@@ -504,7 +513,7 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
                             __syncwarp();
 #pragma unroll
                             for (int g = 0; g < 8; ++g) rc[g] = ld_shared_v4(buf + (uint32_t)lane * 128u + (uint32_t)((g ^ (lane & 7)) << 4));
-                            if (c + 1 < BN / 64 && nc + 64 < N) load_res(c + 1);
+                            if (c + CSTEP < BN / 64 && nc + 64 * CSTEP < N) load_res(c + CSTEP);
                         } else {
 #pragma unroll
                             for (int g = 0; g < 8; ++g) rc[g] = make_uint4(0, 0, 0, 0);
@@ -542,10 +551,10 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
 // host launch
 // ---------------------------------------------------------------------------------------------------
 inline int configure(char *err) {
-    cudaError_t e = cudaFuncSetAttribute(k_gemm_tc<128, 256, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    cudaError_t e = cudaFuncSetAttribute(k_gemm_tc<128, 256, false, 4, CfgStd::EPI_BUFS, CfgStd::EPI_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)CfgStd::SMEM_BYTES);
     if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(k_gemm_tc<128, 256, false, 3, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CfgHbm::SMEM_BYTES);
+        e = cudaFuncSetAttribute(k_gemm_tc<128, 256, false, 3, 2, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CfgHbm::SMEM_BYTES);
     if (e == cudaSuccess)
         e = cudaFuncSetAttribute(k_gemm_tc<128, 64, false, 4, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CfgSmallM::SMEM_BYTES);
     if (e == cudaSuccess)
@@ -605,10 +614,10 @@ inline int launch_gemm(const TmaEncoder &enc, const bf16 *A, const CUtensorMap *
     }
     const int grid = tiles < num_sms() ? tiles : num_sms();
     if (K <= KDL_HBM_CFG_MAX_K)  // HBM-bound: more stores in flight matter more than ring depth
-        launch_k(k_gemm_tc<128, 256, false, 3, 4>, dim3(grid), dim3(NUM_THREADS), CfgHbm::SMEM_BYTES, st, tmA, *tmB, tmOut, tmRes, bias, residual, out,
+        launch_k(k_gemm_tc<128, 256, false, 3, 2, 8>, dim3(grid), dim3(CfgHbm::THREADS), CfgHbm::SMEM_BYTES, st, tmA, *tmB, tmOut, tmRes, bias, residual, out,
                  M, N, K, relu, ConvGeom{0, 0, 0, 0}, ldo, rev);
     else
-        launch_k(k_gemm_tc<128, 256, false>, dim3(grid), dim3(NUM_THREADS), CfgStd::SMEM_BYTES, st, tmA, *tmB, tmOut, tmRes, bias, residual, out, M, N,
+        launch_k(k_gemm_tc<128, 256, false, 4, CfgStd::EPI_BUFS, CfgStd::EPI_WARPS>, dim3(grid), dim3(CfgStd::THREADS), CfgStd::SMEM_BYTES, st, tmA, *tmB, tmOut, tmRes, bias, residual, out, M, N,
                  K, relu, ConvGeom{0, 0, 0, 0}, ldo, rev);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
