@@ -164,7 +164,7 @@ struct KdlModel {
 };
 
 enum ProfClass { PC_RESIZE = 0, PC_CONV1, PC_CONV2, PC_DW, PC_PW_TC_HBM, PC_PW_TC_TENSOR, PC_GEMM_SIMPLE, PC_SUBSAMPLE, PC_POOL, PC_HEAD, PC_SEPFUSED, PC_SEPMID, PC_COUNT };
-static const char *PROF_NAMES[PC_COUNT] = {"k_resize", "k_conv1", "conv2_implicit_gemm", "k_dw3x3", "k_gemm_tc[K<=256,hbm-bound]",
+static const char *PROF_NAMES[PC_COUNT] = {"k_resize", "k_conv1_tc|k_conv1", "conv2_implicit_gemm", "k_dw3x3", "k_gemm_tc[K<=256,hbm-bound]",
                                            "k_gemm_tc[K>=728,tensor-bound]", "k_gemm_simple", "k_subsample2", "k_maxpool_add", "k_gap_partial+k_head_finish",
                                            "k_sepconv_tc[fused dw+pw,hbm-bound]", "k_sepconv_mid[fused dw+pw,tensor-bound]"};
 
