@@ -6,7 +6,7 @@
 Per init (calibrated, calibrated_mild; weights seed 1): pictures = oracle.structured.structured_images(512, seed=3) with
 mixed source sizes, preprocessed by Pillow (the reference's code path), pushed through oracle.xception_oracle in float64.
 Stored: the natural-head logits, the re-centred head biases (oracle.structured.recentre_head on all 512 feature vectors) and
-the logits under that head.  tests/test_gpu_accuracy.py and scripts/report_configs.py compare the GPU against these.
+the logits under that head.  tests/test_gpu_accuracy.py compares the GPU against these.
 """
 import os
 import sys
