@@ -68,7 +68,9 @@ typedef struct KdlTuning {
                                     values (exact in bf16; x/127.5-1 folded into bf16 weights + fp32 bias).  0: the CUDA-core kernel
                                     with fp32 weights (always used for float inputs and the fp32 path).  The ONE switch that
                                     changes bits: conv1's weights are rounded to bf16 like every other layer's */
-    int32_t reserved[6];         /* must be 0 */
+    int32_t dw_tma_store;        /* !=0: the depthwise kernel stages each output tile in shared memory and writes it with one 4-D TMA
+                                    store (2 input stages) instead of 8-byte stores from every thread (3 input stages) */
+    int32_t reserved[5];         /* must be 0 */
 } KdlTuning;
 int kdl_get_tuning(const KdlModel *m, KdlTuning *out);
 int kdl_set_tuning(KdlModel *m, const KdlTuning *t);

@@ -29,7 +29,7 @@ class KdlConfig(ctypes.Structure):
 
 class KdlTuning(ctypes.Structure):
     _fields_ = [("pdl_max_batch", c_int32), ("serpentine", c_int32), ("conv2_shifted_taps", c_int32), ("fused_sepconv", c_int32),
-                ("fused_midflow", c_int32), ("conv1_tc", c_int32), ("reserved", c_int32 * 6)]
+                ("fused_midflow", c_int32), ("conv1_tc", c_int32), ("dw_tma_store", c_int32), ("reserved", c_int32 * 5)]
 
 
 class KdlProfileRow(ctypes.Structure):

@@ -39,6 +39,10 @@ struct Params {
     int rev;         // 1: walk the tiles from the last to the first (the consumer of a tensor larger than L2 starts where its producer stopped)
     uint32_t tile_bytes, stage_bytes;
     int consumer_threads;
+    int tma_store;   // 1: output tiles are staged in shared memory and leave through one 4-D TMA store per tile (2 input stages);
+                     // 0: every thread stores its 8 bytes straight to global memory (3 input stages)
+    int stages;      // input ring depth
+    uint32_t out_bytes;   // TH * TW * 128: one staged output tile
 };
 
 inline Params make_params(int B, int H, int W, int C, int ld, int relu_in) {
@@ -67,9 +71,19 @@ inline Params make_params(int B, int H, int W, int C, int ld, int relu_in) {
     p.total_tiles = B * p.nty * p.ntx * p.nch;
     p.tile_bytes = (uint32_t)(p.BW * p.BH * 128);
     p.stage_bytes = p.tile_bytes + W_BYTES;
+    p.tma_store = 0;
+    p.stages = STAGES;
+    p.out_bytes = (uint32_t)(p.TH * p.TW * 128);
     return p;
 }
-inline uint32_t smem_bytes(const Params &p) { return STAGES * p.stage_bytes + 128 /*barriers*/ + 128 /*align*/; }
+inline uint32_t smem_bytes(const Params &p) {
+    return p.stages * p.stage_bytes + (p.tma_store ? 2 * p.out_bytes : 0) + 128 /*barriers*/ + 128 /*align*/;
+}
+__device__ __forceinline__ void tma_store_4d(const CUtensorMap *tm, uint32_t src, int c0, int c1, int c2, int c3) {
+    asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(tm), "r"(src), "r"(c0),
+                 "r"(c1), "r"(c2), "r"(c3)
+                 : "memory");
+}
 
 __device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap *tm, uint32_t bar, int c0, int c1, int c2, int c3) {
     asm volatile(
@@ -148,20 +162,28 @@ __device__ __forceinline__ void scatter_row(uint32_t rowaddr, const float2 (&wl)
     }
 }
 
-template <bool RELU>
-__global__ void __launch_bounds__(512, 1)
-k_dw_tma(const __grid_constant__ CUtensorMap tmIn, const float *__restrict__ wpad /*[nch][9][64]*/, bf16 *__restrict__ out, Params p) {
+template <bool RELU, bool TMAS = false>
+__global__ void __launch_bounds__(TMAS ? 544 : 512, 1)
+k_dw_tma(const __grid_constant__ CUtensorMap tmIn, const __grid_constant__ CUtensorMap tmOut /*box 64 x TW x TH x 1; used with p.tma_store*/,
+         const float *__restrict__ wpad /*[nch][9][64]*/, bf16 *__restrict__ out, Params p) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (tc::smem_u32(smem_raw) + 127u) & ~127u;
-    const uint32_t bar_base = base + STAGES * p.stage_bytes;
+    const int NST = p.stages;
+    constexpr bool kStore = TMAS;   // p.tma_store, known at compile time (the two variants have different thread counts / register budgets)
+    const uint32_t obuf_base = base + NST * p.stage_bytes;                          // two staged output tiles (tma_store)
+    const uint32_t bar_base = obuf_base + (kStore ? 2u * p.out_bytes : 0u);
     auto full_bar = [&](int s) { return bar_base + 8u * s; };
-    auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+    auto empty_bar = [&](int s) { return bar_base + 8u * (NST + s); };
+    auto ofull_bar = [&](int s) { return bar_base + 8u * (2 * NST + s); };           // consumers -> store thread
+    auto oempty_bar = [&](int s) { return bar_base + 8u * (2 * NST + 2 + s); };      // store thread -> consumers
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_cwarps = p.consumer_threads >> 5;
 
     if (threadIdx.x == 0) {
         tc::prefetch_tmap(&tmIn);
-        for (int s = 0; s < STAGES; ++s) { tc::mbar_init(full_bar(s), 1); tc::mbar_init(empty_bar(s), n_cwarps); }
+        if (kStore) tc::prefetch_tmap(&tmOut);
+        for (int s = 0; s < NST; ++s) { tc::mbar_init(full_bar(s), 1); tc::mbar_init(empty_bar(s), n_cwarps); }
+        for (int s = 0; s < 2; ++s) { tc::mbar_init(ofull_bar(s), n_cwarps); tc::mbar_init(oempty_bar(s), 1); }
         tc::fence_barrier_init();
     }
     __syncthreads();
@@ -185,12 +207,34 @@ k_dw_tma(const __grid_constant__ CUtensorMap tmIn, const float *__restrict__ wpa
                 const uint32_t dst = base + stage * p.stage_bytes;
                 tma_load_4d(dst, &tmIn, full_bar(stage), ch * CB, tx * p.TW - 1, ty * p.TH - 1, b);
                 bulk_load_1d(dst + p.tile_bytes, wpad + (size_t)ch * 9 * CB, W_BYTES, full_bar(stage));
-                if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+                if (++stage == NST) { stage = 0; phase ^= 1u; }
             }
         }
         return;
     }
-    if (warp > n_cwarps) return;
+    if (warp == n_cwarps + 1) {
+        // ================= store warp (tma_store): one 4-D TMA store per finished output tile =================
+        if (lane == 0 && kStore) {
+            int it = 0;
+            for (int ti = blockIdx.x; ti < p.total_tiles; ti += gridDim.x, ++it) {
+                const int t = p.rev ? p.total_tiles - 1 - ti : ti;
+                const int ch = t % p.nch;
+                int s = t / p.nch;
+                const int tx = s % p.ntx; s /= p.ntx;
+                const int ty = s % p.nty;
+                const int b = s / p.nty;
+                const int os = it & 1;
+                tc::mbar_wait(ofull_bar(os), (uint32_t)((it >> 1) & 1));
+                tma_store_4d(&tmOut, obuf_base + os * p.out_bytes, ch * CB, tx * p.TW, ty * p.TH, b);   // clipped at the tensor edges
+                tc::bulk_commit();
+                tc::bulk_wait_read<0>();             // ~1 us, while the consumers work on the next tile in the other buffer
+                tc::mbar_arrive(oempty_bar(os));     // the store has finished READING its buffer: hand it back
+            }
+            tc::bulk_wait_all<0>();
+        }
+        return;
+    }
+    if (warp > n_cwarps + 1) return;
 
     // ================= consumers =================
     const int cg = threadIdx.x & 15;           // 4-channel group inside the 64-channel chunk
@@ -200,13 +244,16 @@ k_dw_tma(const __grid_constant__ CUtensorMap tmIn, const float *__restrict__ wpa
     const bool active = strip < p.NS;
     int stage = 0;
     uint32_t phase = 0;
-    for (int ti = blockIdx.x; ti < p.total_tiles; ti += gridDim.x) {
+    int it = 0;
+    for (int ti = blockIdx.x; ti < p.total_tiles; ti += gridDim.x, ++it) {
         const int t = p.rev ? p.total_tiles - 1 - ti : ti;
         const int ch = t % p.nch;
         int s = t / p.nch;
         const int tx = s % p.ntx; s /= p.ntx;
         const int ty = s % p.nty;
         const int b = s / p.nty;
+        const int os = it & 1;
+        if (kStore) tc::mbar_wait(oempty_bar(os), (uint32_t)((it >> 1) & 1) ^ 1u);   // its store of two tiles ago has read the buffer
         tc::mbar_wait(full_bar(stage), phase);
         const int c = ch * CB + cg * 4;
         const int x0 = tx * p.TW + 2 * cp;                 // first of this thread's two output columns
@@ -226,6 +273,10 @@ k_dw_tma(const __grid_constant__ CUtensorMap tmIn, const float *__restrict__ wpa
             const bool st1 = (2 * cp + 1 < p.TW) && (x0 + 1 < p.W);
             bf16 *o = out + (((size_t)b * p.H + (size_t)ty * p.TH + y_lo) * p.W + x0) * p.ld + c;
             const size_t orow = (size_t)p.W * p.ld;
+            // staged output tile: [TH][TW][64 channels], 128 bytes per pixel, the layout the 4-D store box expects
+            uint32_t so = obuf_base + os * p.out_bytes + ((uint32_t)(y_lo * p.TW) + 2u * cp) * 128u + (uint32_t)cg * 8u;
+            const uint32_t so_row = (uint32_t)p.TW * 128u;
+            constexpr bool via_smem = kStore;
             // accumulators of output rows (r-1, r, r+1) relative to the input row r being scattered; [col][lo/hi]
             float2 aA[2][2], aB[2][2], aC[2][2];
             // staged row index = tile-relative input row + 1; thread's columns start at staged column 2*cp
@@ -235,9 +286,15 @@ k_dw_tma(const __grid_constant__ CUtensorMap tmIn, const float *__restrict__ wpa
                 uint2 v0, v1;
                 v0.x = tc::pack_bf16(aA[0][0].x, aA[0][0].y); v0.y = tc::pack_bf16(aA[0][1].x, aA[0][1].y);
                 v1.x = tc::pack_bf16(aA[1][0].x, aA[1][0].y); v1.y = tc::pack_bf16(aA[1][1].x, aA[1][1].y);
-                st_stream(o, v0);
-                if (st1) st_stream(o + p.ld, v1);
-                o += orow;
+                if (via_smem) {
+                    asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(so), "r"(v0.x), "r"(v0.y) : "memory");
+                    if (st1) asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(so + 128u), "r"(v1.x), "r"(v1.y) : "memory");
+                    so += so_row;
+                } else {
+                    st_stream(o, v0);
+                    if (st1) st_stream(o + p.ld, v1);
+                    o += orow;
+                }
             };
             auto rotate = [&]() {
 #pragma unroll
@@ -264,9 +321,13 @@ k_dw_tma(const __grid_constant__ CUtensorMap tmIn, const float *__restrict__ wpa
             scatter_row<RELU, true, false, false>(rowaddr, wl, wh, aA, aB, aC);
             store_row();
         }
+        if (kStore) tc::fence_proxy_async_smem();   // the staged tile is read by the async proxy (TMA store)
         __syncwarp();
-        if (lane == 0) tc::mbar_arrive(empty_bar(stage));
-        if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        if (lane == 0) {
+            tc::mbar_arrive(empty_bar(stage));
+            if (kStore) tc::mbar_arrive(ofull_bar(os));
+        }
+        if (++stage == NST) { stage = 0; phase ^= 1u; }
     }
 }
 
@@ -284,9 +345,11 @@ inline bool encode_input_map(const tc::TmaEncoder &enc, CUtensorMap *tm, const v
 }
 
 inline int configure(char *err) {
-    cudaError_t e = cudaFuncSetAttribute(k_dw_tma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * (int)(TILE_BUDGET + W_BYTES) + 256);
-    if (e == cudaSuccess)
-        e = cudaFuncSetAttribute(k_dw_tma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * (int)(TILE_BUDGET + W_BYTES) + 256);
+    const int max_smem = 227 * 1024;   // direct stores: 3 x (tile + weights); TMA store: 2 x (tile + weights) + 2 x output tile
+    cudaError_t e = cudaFuncSetAttribute(k_dw_tma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_dw_tma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_dw_tma<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_dw_tma<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
     if (e != cudaSuccess) {
         snprintf(err, 512, "cudaFuncSetAttribute(k_dw_tma): %s", cudaGetErrorString(e));
         return KDL_ECUDA;
@@ -294,11 +357,29 @@ inline int configure(char *err) {
     return KDL_OK;
 }
 
+inline bool encode_output_map(const tc::TmaEncoder &enc, CUtensorMap *tm, void *out, const Params &p) {
+    cuuint64_t dims[4] = {(cuuint64_t)p.C, (cuuint64_t)p.W, (cuuint64_t)p.H, (cuuint64_t)p.B};
+    cuuint64_t strides[3] = {(cuuint64_t)p.ld * 2, (cuuint64_t)p.W * p.ld * 2, (cuuint64_t)p.H * p.W * p.ld * 2};
+    cuuint32_t box[4] = {(cuuint32_t)CB, (cuuint32_t)p.TW, (cuuint32_t)p.TH, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    return enc.fn(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, out, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 inline int launch(const tc::TmaEncoder &enc, const bf16 *in, const float *wpad, bf16 *out, int B, int H, int W, int C, int ld,
-                  int relu_in, cudaStream_t st, char *err, int rev = 0) {
+                  int relu_in, cudaStream_t st, char *err, int rev = 0, int tma_store = 0) {
     Params p = make_params(B, H, W, C, ld, relu_in);
     p.rev = rev;
-    CUtensorMap tm;
+    if (tma_store && p.TW <= 256 && p.TH <= 256) {
+        p.tma_store = 1;
+        p.stages = 2;
+        if (smem_bytes(p) > 227u * 1024u) { p.tma_store = 0; p.stages = STAGES; }
+    }
+    CUtensorMap tm, tmo;
+    if (p.tma_store && !encode_output_map(enc, &tmo, out, p)) {
+        snprintf(err, 512, "cuTensorMapEncodeTiled(4d) failed for depthwise output [%d,%d,%d,%d] box [%d,%d]", B, H, W, C, p.TW, p.TH);
+        return KDL_ECUDA;
+    }
     if (!encode_input_map(enc, &tm, in, p)) {
         snprintf(err, 512, "cuTensorMapEncodeTiled(4d) failed for depthwise input [%d,%d,%d,%d] box [%d,%d]", B, H, W, C, p.BW, p.BH);
         return KDL_ECUDA;
@@ -308,11 +389,18 @@ inline int launch(const tc::TmaEncoder &enc, const bf16 *in, const float *wpad, 
     if (per_sm < 1) per_sm = 1;
     const int nsm = tc::num_sms() * per_sm;
     const int grid = p.total_tiles < nsm ? p.total_tiles : nsm;
-    if (relu_in) launch_k(k_dw_tma<true>, dim3(grid), dim3(p.consumer_threads + 32), smem_bytes(p), st, tm, wpad, out, p);
-    else launch_k(k_dw_tma<false>, dim3(grid), dim3(p.consumer_threads + 32), smem_bytes(p), st, tm, wpad, out, p);
+    if (!p.tma_store) tmo = tm;   // never dereferenced
+    const int threads = p.consumer_threads + (p.tma_store ? 64 : 32);   // + producer warp (+ store warp)
+    if (p.tma_store) {
+        if (relu_in) launch_k(k_dw_tma<true, true>, dim3(grid), dim3(threads), smem_bytes(p), st, tm, tmo, wpad, out, p);
+        else launch_k(k_dw_tma<false, true>, dim3(grid), dim3(threads), smem_bytes(p), st, tm, tmo, wpad, out, p);
+    } else {
+        if (relu_in) launch_k(k_dw_tma<true>, dim3(grid), dim3(threads), smem_bytes(p), st, tm, tmo, wpad, out, p);
+        else launch_k(k_dw_tma<false>, dim3(grid), dim3(threads), smem_bytes(p), st, tm, tmo, wpad, out, p);
+    }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
-        snprintf(err, 512, "k_dw_tma launch (B=%d H=%d C=%d threads=%d smem=%u): %s", B, H, C, p.consumer_threads + 32, smem_bytes(p),
+        snprintf(err, 512, "k_dw_tma launch (B=%d H=%d C=%d threads=%d smem=%u): %s", B, H, C, threads, smem_bytes(p),
                  cudaGetErrorString(e));
         return KDL_ECUDA;
     }

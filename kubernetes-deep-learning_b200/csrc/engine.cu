@@ -202,6 +202,7 @@ static KdlTuning default_tuning() {
     t.conv2_shifted_taps = 0;
     t.fused_sepconv = 1;
     t.conv1_tc = 1;
+    t.dw_tma_store = 0;
     t.fused_midflow = 0;   // built, bit-identical, measured: 246 us per 728->728 layer at batch 256 against 165 us for k_dw_tma + k_gemm_tc
     return t;
 }
@@ -282,7 +283,7 @@ template <typename T> struct Runner {
         dim3 grid((vec + 127) / 128, (H + rows - 1) / rows, B);
         prof_open(m, st, PC_DW, 18.0 * B * H * H * C, 2.0 * B * H * H * C * sizeof(T) + 36.0 * C, "dw H=%d C=%d relu=%d", H, C, relu_in);
         if (use_tc()) {
-            int rc = dwt::launch(m->tma, (const bf16 *)in, wpad, (bf16 *)out, B, H, H, C, ld(C), relu_in, st, m->err, flip());
+            int rc = dwt::launch(m->tma, (const bf16 *)in, wpad, (bf16 *)out, B, H, H, C, ld(C), relu_in, st, m->err, flip(), m->tune.dw_tma_store);
             prof_close(m, st);
             if (rc != KDL_OK) return rc;
             m->launches++;

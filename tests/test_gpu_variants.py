@@ -29,7 +29,7 @@ def test_kernel_variants_are_bit_identical():
     base = _logits({}, W, u8)
     assert len({tuple(r) for r in base.round(3).tolist()}) == 5          # five pictures, five different answers
     for tuning in ({"fused_sepconv": 0}, {"conv2_shifted_taps": 1}, {"pdl_max_batch": 1 << 20}, {"pdl_max_batch": 0},
-                   {"serpentine": 0}, {"fused_midflow": 1}, {"fused_midflow": 0, "fused_sepconv": 0}):
+                   {"serpentine": 0}, {"dw_tma_store": 1}, {"fused_midflow": 1}, {"fused_midflow": 0, "fused_sepconv": 0}):
         got = _logits(tuning, W, u8)
         np.testing.assert_array_equal(got, base, err_msg=str(tuning))
 
