@@ -45,7 +45,7 @@ struct Params {
     uint32_t out_bytes;   // TH * TW * 128: one staged output tile
 };
 
-inline Params make_params(int B, int H, int W, int C, int ld, int relu_in) {
+inline Params make_params(int B, int H, int W, int C, int ld, int relu_in, uint32_t tile_budget = TILE_BUDGET, int max_ns = 3) {
     Params p;
     p.B = B; p.H = H; p.W = W; p.C = C; p.ld = ld; p.relu_in = relu_in; p.rev = 0;
     int ntx = (W + 19) / 20;                 // tiles <= 20 columns wide: 10 column pairs x 16 channel groups = 160 threads per strip
@@ -53,7 +53,7 @@ inline Params make_params(int B, int H, int W, int C, int ld, int relu_in) {
     p.ntx = ntx;
     p.CP = (p.TW + 1) / 2;
     p.BW = 2 * p.CP + 2;
-    int max_bh = (int)(TILE_BUDGET / (uint32_t)(p.BW * 128));
+    int max_bh = (int)(tile_budget / (uint32_t)(p.BW * 128));
     int th_max = max_bh - 2 < 1 ? 1 : max_bh - 2;
     if (th_max > H) th_max = H;
     p.nty = (H + th_max - 1) / th_max;
@@ -61,7 +61,7 @@ inline Params make_params(int B, int H, int W, int C, int ld, int relu_in) {
     p.BH = p.TH + 2;
     int per_strip = 16 * p.CP;
     int ns = 480 / per_strip;                // strips only re-load their 2 halo rows (the scatter is peeled), so 3 is cheap
-    if (ns > 3) ns = 3;
+    if (ns > max_ns) ns = max_ns;
     if (ns > p.TH) ns = p.TH;
     if (ns < 1) ns = 1;
     p.RS = (p.TH + ns - 1) / ns;
@@ -162,10 +162,9 @@ __device__ __forceinline__ void scatter_row(uint32_t rowaddr, const float2 (&wl)
     }
 }
 
-template <bool RELU, bool TMAS = false>
-__global__ void __launch_bounds__(TMAS ? 544 : 512, 1)
-k_dw_tma(const __grid_constant__ CUtensorMap tmIn, const __grid_constant__ CUtensorMap tmOut /*box 64 x TW x TH x 1; used with p.tma_store*/,
-         const float *__restrict__ wpad /*[nch][9][64]*/, bf16 *__restrict__ out, Params p) {
+template <bool RELU, bool TMAS>
+__device__ __forceinline__ void dw_body(const CUtensorMap &tmIn, const CUtensorMap &tmOut, const float *__restrict__ wpad, bf16 *__restrict__ out,
+                                        const Params &p) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (tc::smem_u32(smem_raw) + 127u) & ~127u;
     const int NST = p.stages;
@@ -329,6 +328,20 @@ k_dw_tma(const __grid_constant__ CUtensorMap tmIn, const __grid_constant__ CUten
         }
         if (++stage == NST) { stage = 0; phase ^= 1u; }
     }
+}
+
+template <bool RELU, bool TMAS = false>
+__global__ void __launch_bounds__(TMAS ? 544 : 512, 1)
+k_dw_tma(const __grid_constant__ CUtensorMap tmIn, const __grid_constant__ CUtensorMap tmOut /*box 64 x TW x TH x 1; used with p.tma_store*/,
+         const float *__restrict__ wpad /*[nch][9][64]*/, bf16 *__restrict__ out, const __grid_constant__ Params p) {
+    dw_body<RELU, TMAS>(tmIn, tmOut, wpad, out, p);
+}
+// "slim" build of the same body for the co-residency probe (engine.cu, probe builds): at most 96 registers per thread, so that a
+// 352-thread CTA (two strips + producer) fits next to a 128-register GEMM CTA on one SM
+template <bool RELU>
+__global__ void __maxnreg__(96)
+k_dw_tma_slim(const __grid_constant__ CUtensorMap tmIn, const float *__restrict__ wpad, bf16 *__restrict__ out, const __grid_constant__ Params p) {
+    dw_body<RELU, false>(tmIn, tmIn, wpad, out, p);
 }
 
 // host -------------------------------------------------------------------------------------------------

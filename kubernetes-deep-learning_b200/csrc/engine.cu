@@ -1262,3 +1262,80 @@ extern "C" int kdl_sep_prof_read(unsigned long long *out) {
     return cudaMemcpyFromSymbol(out, kdl::sepc::g_sep_prof, sizeof(unsigned long long) * 4 * 160 * 16) == cudaSuccess ? 0 : -2;
 }
 #endif
+
+#ifdef KDL_MID_PROF
+// Probe (probe builds only): can a pointwise GEMM and a depthwise kernel of DIFFERENT half-batches share the SMs?  Runs, on the
+// middle-flow shape (B images of 19 x 19 x 728, pitch 768), `iters` rounds of { GEMM(A) ; depthwise(B) } three ways -- the product
+// kernels back to back on one stream, the slim kernels (3-stage GEMM at <= 128 registers; depthwise with two strips, ~22 KB tiles,
+// 2 stages, <= 96 registers: 222 KB of shared memory and ~58 k registers together) back to back, and the slim kernels on two streams
+// so that their CTAs can be co-resident -- and returns the three times per round in microseconds.
+extern "C" int kdl_corun_probe(int B, int iters, float *out_us /*[3]*/) {
+    using namespace kdl;
+    char err[512];
+    tc::TmaEncoder enc;
+    enc.init();
+    if (!enc.ok() || tc::configure(err) || dwt::configure(err)) return -2;
+    const int H = 19, C = 728, LD = 768, M = B * H * H;
+    bf16 *X[2], *T[2], *U[2], *Wt;
+    float *bias, *wpad;
+    for (int i = 0; i < 2; ++i) {
+        cudaMalloc(&X[i], (size_t)(M + 256) * LD * 2); cudaMalloc(&T[i], (size_t)(M + 256) * LD * 2); cudaMalloc(&U[i], (size_t)(M + 256) * LD * 2);
+        cudaMemset(X[i], 0x3c, (size_t)(M + 256) * LD * 2); cudaMemset(T[i], 0x3c, (size_t)(M + 256) * LD * 2);
+    }
+    cudaMalloc(&Wt, (size_t)768 * 768 * 2); cudaMemset(Wt, 0x3c, (size_t)768 * 768 * 2);
+    cudaMalloc(&bias, 768 * 4); cudaMemset(bias, 0, 768 * 4);
+    cudaMalloc(&wpad, 12 * 9 * 64 * 4); cudaMemset(wpad, 0, 12 * 9 * 64 * 4);
+    CUtensorMap tmB;
+    enc.encode_2d(&tmB, Wt, C, C, 768 * 2, tc::BLOCK_K, tc::BLOCK_N, 128);
+    cudaFuncSetAttribute(tc::k_gemm_tc_slim, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tc::CfgSlim::SMEM_BYTES);
+    cudaFuncSetAttribute(dwt::k_dw_tma_slim<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+    cudaStream_t s1, s2;
+    cudaStreamCreateWithFlags(&s1, cudaStreamNonBlocking); cudaStreamCreateWithFlags(&s2, cudaStreamNonBlocking);
+    cudaEvent_t e0, e1, j2;
+    cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreateWithFlags(&j2, cudaEventDisableTiming);
+
+    auto gemm_slim = [&](int h, cudaStream_t st) {
+        CUtensorMap tmA, tmOut;
+        enc.encode_2d(&tmA, T[h], C, M, LD * 2, tc::BLOCK_K, tc::BLOCK_M, 128);
+        enc.encode_2d(&tmOut, U[h], C, M, LD * 2, 64, 32, 128);
+        const int tiles = ((M + 127) / 128) * 3;
+        const int grid = tiles < tc::num_sms() ? tiles : tc::num_sms();
+        tc::k_gemm_tc_slim<<<grid, 192, tc::CfgSlim::SMEM_BYTES, st>>>(tmA, tmB, tmOut, tmOut, bias, nullptr, U[h], M, C, C, 1, LD, 0);
+    };
+    auto dw_slim = [&](int h, cudaStream_t st) {
+        dwt::Params p = dwt::make_params(B, H, H, C, LD, 0, 22528, 2);
+        p.stages = 2;
+        CUtensorMap tm;
+        dwt::encode_input_map(enc, &tm, X[h], p);
+        const int grid = p.total_tiles < tc::num_sms() ? p.total_tiles : tc::num_sms();
+        dwt::k_dw_tma_slim<false><<<grid, p.consumer_threads + 32, dwt::smem_bytes(p), st>>>(tm, wpad, T[h], p);
+    };
+    auto timed = [&](int mode) -> float {
+        for (int w = 0; w < 2 + iters; ++w) {
+            if (w == 2) { cudaDeviceSynchronize(); cudaEventRecord(e0, s1); }
+            if (mode == 0) {
+                tc::launch_gemm(enc, T[0], &tmB, bias, nullptr, U[0], M, C, C, 1, s1, err, LD, LD);
+                dwt::launch(enc, X[1], wpad, T[1], B, H, H, C, LD, 0, s1, err);
+            } else if (mode == 1) {
+                gemm_slim(0, s1);
+                dw_slim(1, s1);
+            } else {
+                gemm_slim(0, s1);
+                dw_slim(1, s2);
+            }
+        }
+        if (mode == 2) { cudaEventRecord(j2, s2); cudaStreamWaitEvent(s1, j2, 0); }
+        cudaEventRecord(e1, s1);
+        cudaEventSynchronize(e1);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        return ms * 1e3f / iters;
+    };
+    for (int mode = 0; mode < 3; ++mode) out_us[mode] = timed(mode);
+    cudaError_t e = cudaDeviceSynchronize();
+    for (int i = 0; i < 2; ++i) { cudaFree(X[i]); cudaFree(T[i]); cudaFree(U[i]); }
+    cudaFree(Wt); cudaFree(bias); cudaFree(wpad);
+    cudaStreamDestroy(s1); cudaStreamDestroy(s2);
+    return e == cudaSuccess ? 0 : -2;
+}
+#endif

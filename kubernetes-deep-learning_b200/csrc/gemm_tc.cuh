@@ -286,12 +286,10 @@ __device__ __forceinline__ uint4 epi8(const uint32_t *acc, uint32_t bias_addr, i
 // ---------------------------------------------------------------------------------------------------
 // the kernel
 // ---------------------------------------------------------------------------------------------------
-template <int SW, int BN, bool CONV, int NST = (CONV ? 12 : 4), int EB = 2, int EW = 4>
-__global__ void __launch_bounds__((2 + EW) * 32, 1)
-k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-          const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes /*residual, box 64 x 128; L2 prefetch only*/,
-          const float *__restrict__ bias, const bf16 *residual, bf16 *out, int M, int N, int K, int relu, ConvGeom cg,
-          int ldo /*row pitch of out / residual in elements*/, int rev = 0 /*1: walk the tiles from the last to the first*/) {
+template <int SW, int BN, bool CONV, int NST, int EB, int EW>
+__device__ __forceinline__ void gemm_tc_body(const CUtensorMap &tmA, const CUtensorMap &tmB, const CUtensorMap &tmOut, const CUtensorMap &tmRes,
+                                             const float *__restrict__ bias, const bf16 *residual, bf16 *out, int M, int N, int K, int relu,
+                                             ConvGeom cg, int ldo, int rev) {
     typedef Cfg<SW, BN, CONV, NST, EB, EW> C;
     constexpr int STAGES = C::STAGES;
     constexpr int BK = C::BLOCK_K;
@@ -546,6 +544,24 @@ k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         tmem_dealloc(tmem_base, C::TMEM_COLS);
     }
 }
+
+template <int SW, int BN, bool CONV, int NST = (CONV ? 12 : 4), int EB = 2, int EW = 4>
+__global__ void __launch_bounds__((2 + EW) * 32, 1)
+k_gemm_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+          const __grid_constant__ CUtensorMap tmOut, const __grid_constant__ CUtensorMap tmRes /*residual, box 64 x 128; L2 prefetch only*/,
+          const float *__restrict__ bias, const bf16 *residual, bf16 *out, int M, int N, int K, int relu, ConvGeom cg,
+          int ldo /*row pitch of out / residual in elements*/, int rev = 0 /*1: walk the tiles from the last to the first*/) {
+    gemm_tc_body<SW, BN, CONV, NST, EB, EW>(tmA, tmB, tmOut, tmRes, bias, residual, out, M, N, K, relu, cg, ldo, rev);
+}
+// "slim" build for the co-residency probe (engine.cu, probe builds): 3-stage ring (178 KB of shared memory) and at most 128 registers
+// per thread, so that a depthwise CTA fits on the same SM
+__global__ void __maxnreg__(128)
+k_gemm_tc_slim(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmOut,
+               const __grid_constant__ CUtensorMap tmRes, const float *__restrict__ bias, const bf16 *residual, bf16 *out, int M, int N, int K,
+               int relu, int ldo, int rev) {
+    gemm_tc_body<128, 256, false, 3, 2, 4>(tmA, tmB, tmOut, tmRes, bias, residual, out, M, N, K, relu, ConvGeom{0, 0, 0, 0}, ldo, rev);
+}
+typedef Cfg<128, 256, false, 3, 2, 4> CfgSlim;
 
 // ---------------------------------------------------------------------------------------------------
 // host launch
