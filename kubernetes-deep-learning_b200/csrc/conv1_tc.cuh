@@ -23,12 +23,15 @@ constexpr int BM = 128;
 constexpr int NA = 6;                              // A-tile ring
 constexpr int TEAMS = 3;                           // gather teams of 4 warps; team g builds the CTA's tiles g, g+3, g+6, ...
 constexpr int GATHER_WARPS = 4 * TEAMS;
-constexpr int NUM_THREADS_C1 = (6 + GATHER_WARPS) * 32;
+constexpr int EPI_SETS = 2;                        // epilogue warp sets (4 warps each); set h drains accumulator buffer h = every other tile.
+                                                   // One set was the bottleneck: ~100 dependent instructions + three barrier round trips per tile
+constexpr int FIRST_GATHER_WARP = 2 + 4 * EPI_SETS;
+constexpr int NUM_THREADS_C1 = (FIRST_GATHER_WARP + GATHER_WARPS) * 32;
 static_assert(NA % TEAMS == 0, "a ring slot always belongs to the same team");
 constexpr uint32_t A_BYTES = BM * 128;             // 16 KB per stage
 constexpr uint32_t W_BYTES = 32 * 128;             // [32 co][64 k] bf16, k >= 27 zero
 constexpr int EB = 4;                              // output staging buffers per epilogue warp (bulk stores in flight: the kernel writes 5 bytes per byte read)
-constexpr uint32_t EPI_BYTES = 4 * EB * 2048;      // per epilogue warp: EB x (32 rows x 64 B)
+constexpr uint32_t EPI_BYTES = 4 * EPI_SETS * EB * 2048;   // per epilogue warp: EB x (32 rows x 64 B)
 constexpr uint32_t SMEM_BYTES = NA * A_BYTES + W_BYTES + EPI_BYTES + 128 /*bias*/ + 256 /*barriers*/ + 1024 /*align*/;
 
 __device__ __forceinline__ void bulk_store_1d(void *gdst, uint32_t ssrc, uint32_t bytes) {
@@ -103,13 +106,14 @@ k_conv1_tc(const uint8_t *__restrict__ in /*[B,S,S,3]*/, const __grid_constant__
                 if (++as == NA) { as = 0; aph ^= 1u; }
             }
         }
-    } else if (warp < 6) {
-        // ================= epilogue (warps 2..5; TMEM lane quarter = warp % 4) =================
+    } else if (warp < FIRST_GATHER_WARP) {
+        // ================= epilogue (warps 2..9; TMEM lane quarter = warp % 4; set = (warp - 2) / 4 takes the tiles of its accumulator) =================
         const int q = warp & 3;
+        const int set = (warp - 2) >> 2;
         const uint32_t ebuf = epi_base + (uint32_t)(warp - 2) * (uint32_t)(EB * 2048);
         uint32_t n_store = 0;
-        int it = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+        for (int it = set; blockIdx.x + it * (int)gridDim.x < num_tiles; it += EPI_SETS) {
+            const int tile = blockIdx.x + it * (int)gridDim.x;
             const int acc = it & 1;
             mbar_wait(tfull_bar(acc), (uint32_t)((it >> 1) & 1));
             tc_fence_after();
@@ -138,12 +142,12 @@ k_conv1_tc(const uint8_t *__restrict__ in /*[B,S,S,3]*/, const __grid_constant__
         }
         if (lane == 0) bulk_wait_all<0>();
     } else {
-        // ================= gather warps (6..17): three teams of 128 threads, one output pixel per thread =================
+        // ================= gather warps (10..21): three teams of 128 threads, one output pixel per thread =================
         // The source words of a team's NEXT tile are requested before the current tile is converted and stored, and the three teams
         // work on different tiles: about six tiles' loads are in flight per SM, which is what hides the ~1 us global-load latency
         // behind the ~0.3 us a tile may take at the HBM rate.
-        const int team = (warp - 6) >> 2;
-        const int gt = threadIdx.x - 6 * 32 - team * 128;      // A-tile row
+        const int team = (warp - FIRST_GATHER_WARP) >> 2;
+        const int gt = threadIdx.x - FIRST_GATHER_WARP * 32 - team * 128;      // A-tile row
         const uint32_t sw = (uint32_t)gt & 7u;
         const long long hw = (long long)Ho * Ho;
         struct Words { uint32_t w[9]; unsigned sh[3]; bool ok; };
