@@ -20,11 +20,13 @@ constexpr int STAGES = 4;
 constexpr uint32_t MAX_STAGE_BYTES = 2 * 256 * ROWB;  // two TMA boxes of <= 256 rows
 constexpr uint32_t W_BYTES = 9 * COUT * ROWB;       // 36 KB
 constexpr uint32_t BIAS_BYTES = COUT * 4;
-constexpr uint32_t EPI_BYTES = 4 * 2 * 4096;        // per epilogue warp: 2 x (32 rows x 128 B), linear (bulk-store source)
+constexpr int EPI_SETS = 2;                         // epilogue warp sets of 4; set h drains accumulator buffer h = every other tile
+constexpr int THREADS_C2 = (2 + 4 * EPI_SETS) * 32;
+constexpr uint32_t EPI_BYTES = 4 * EPI_SETS * 4096;   // per epilogue warp: 32 rows x 128 B, linear (bulk-store source)
 constexpr uint32_t SMEM_BYTES = STAGES * MAX_STAGE_BYTES + W_BYTES + BIAS_BYTES + EPI_BYTES + 256 + 1024;
 static_assert(SMEM_BYTES <= 232448, "exceeds 227 KB");
 
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+__global__ void __launch_bounds__(THREADS_C2, 1)
 k_conv3x3_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const float *__restrict__ bias,
              bf16 *__restrict__ out, bf16 *__restrict__ sub /*nullable: compact copy of the even pixels*/, int M, int relu, ConvGeom cg,
              int box_rows) {
@@ -108,14 +110,14 @@ k_conv3x3_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
         }
     } else {
         const int q = warp & 3;
+        const int set = (warp - 2) >> 2;
         const int et = threadIdx.x - 64;
         if (et < COUT) asm volatile("st.shared.f32 [%0], %1;" ::"r"(bias_base + 4u * et), "f"(__ldg(bias + et)) : "memory");
-        named_bar_sync(1, 128);
-        int it = 0;
+        named_bar_sync(1, 128 * EPI_SETS);
         const int hw = cg.Hin * cg.Win;
-        const uint32_t ebuf = epi_base + (uint32_t)(warp - 2) * 8192u;
-        uint32_t n_store = 0;
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+        const uint32_t ebuf = epi_base + (uint32_t)(warp - 2) * 4096u;
+        for (int it = set; blockIdx.x + it * (int)gridDim.x < num_tiles; it += EPI_SETS) {
+            const int tile = blockIdx.x + it * (int)gridDim.x;
             const int acc = it & 1;
             const uint32_t acc_phase = (it >> 1) & 1;
             const int row = tile * BLOCK_M + q * 32 + lane;
@@ -137,8 +139,8 @@ k_conv3x3_tc(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CU
             // are consecutive, and so are their outputs except for the two skipped columns at the end of an image row: at most two
             // contiguous runs [0, n1) and [s2, s2 + n2) of lanes, each one bulk store.
             const bool valid = row < M && y < cg.Hout && x < cg.Wout;
-            const uint32_t buf = ebuf + (n_store++ & 1u) * 4096u;
-            if (lane == 0) bulk_wait_read<1>();   // one store group per tile: the group that read this buffer two tiles ago is done
+            const uint32_t buf = ebuf;
+            if (lane == 0) bulk_wait_read<0>();   // this warp's previous store (two tiles ago: the other set took the tile between) has read the buffer
             __syncwarp();
             bf16 *os = (sub && valid && !(y & 1) && !(x & 1))
                            ? sub + ((size_t)(b * ((cg.Hout + 1) >> 1) + (y >> 1)) * ((cg.Wout + 1) >> 1) + (x >> 1)) * COUT
@@ -206,7 +208,7 @@ inline int launch(const TmaEncoder &enc, const bf16 *in, const CUtensorMap *tmB,
     }
     const int tiles = (M + BLOCK_M - 1) / BLOCK_M;
     const int grid = tiles < num_sms() ? tiles : num_sms();
-    launch_k(k_conv3x3_tc, dim3(grid), dim3(NUM_THREADS), SMEM_BYTES, st, tmA, *tmB, bias, out, sub, M, relu,
+    launch_k(k_conv3x3_tc, dim3(grid), dim3(THREADS_C2), SMEM_BYTES, st, tmA, *tmB, bias, out, sub, M, relu,
              ConvGeom{Hin, Win, Hin - 2, Win - 2}, box_rows);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
