@@ -64,3 +64,29 @@ def test_gateway_labels_match_reference_order():
     from kdl_b200 import gateway
     assert gateway.labels == ['dress', 'hat', 'longsleeve', 'outwear', 'pants', 'shirt', 'shoes', 'shorts',
                               'skirt', 't-shirt']
+
+
+def test_ctypes_structs_mirror_the_header_field_for_field():
+    """KdlConfig / KdlTuning / KdlProfileRow in _lib.py must list the same fields, in the same order and with the same array
+    lengths, as include/kdl.h -- a silent mismatch would shift every kernel-selection switch by one slot."""
+    import re
+    import ctypes
+    import kdl_b200  # noqa: F401
+    from kdl_b200 import _lib
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = open(os.path.join(root, "include", "kdl.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    for name, cls in (("KdlConfig", _lib.KdlConfig), ("KdlTuning", _lib.KdlTuning), ("KdlProfileRow", _lib.KdlProfileRow)):
+        body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (name, name), hdr, flags=re.S).group(1)
+        want = []
+        for decl in body.split(";"):
+            m = re.match(r"\s*(\w+)\s+(\w+)(?:\[(\d+)\])?\s*$", decl)
+            if m:
+                want.append((m.group(2), m.group(1), int(m.group(3)) if m.group(3) else 0))
+        got = []
+        for fname, ftype in cls._fields_:
+            n = ftype._length_ if hasattr(ftype, "_length_") else 0
+            base = ftype._type_ if n else ftype
+            cname = {ctypes.c_int32: "int32_t", ctypes.c_float: "float", ctypes.c_double: "double", ctypes.c_char: "char"}[base]
+            got.append((fname, cname, n))
+        assert got == want, (name, got, want)
