@@ -32,6 +32,7 @@ constexpr int NHALF = 384;                    // output columns per work item
 constexpr int NSUB = 192;                     // columns per MMA instruction (two per k-step)
 constexpr int NX = 2, NA = 2, NB = 2;
 constexpr int DW_WARPS = 10;
+constexpr int DW_RS = 4;                      // output rows per depthwise strip (compile time: the row loop is fully unrolled)
 constexpr int NUM_THREADS_MID = (6 + DW_WARPS) * 32;
 constexpr uint32_t X_TILE_MAX = 27 * 1024;    // largest staged halo tile: rows x (W + 2) x 128 bytes
 constexpr uint32_t DWW_BYTES = 9 * CB * 4;
@@ -124,6 +125,49 @@ __device__ __forceinline__ void scatter_px(const dwt::Px (&in)[4], const float2 
         } else {
             aC[j][0] = make_float2(0.f, 0.f);
             aC[j][1] = make_float2(0.f, 0.f);
+        }
+    }
+}
+
+// One input row of a strip, straight-line: which of the three tap rows it feeds is known at compile time (HAS_*), whether the image
+// boundary cancels its upward (a) / downward (c) contribution is a warp-uniform run-time flag.
+template <bool HAS_A, bool HAS_B, bool HAS_C>
+__device__ __forceinline__ void scatter_rt(const dwt::Px (&in)[4], const float2 (&wl)[9], const float2 (&wh)[9], float2 (&aA)[2][2],
+                                           float2 (&aB)[2][2], float2 (&aC)[2][2], bool a, bool c) {
+    if (HAS_A && a) {
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int kx = 0; kx < 3; ++kx) {
+                aA[j][0] = ffma2(in[j + kx].lo, wl[6 + kx], aA[j][0]);
+                aA[j][1] = ffma2(in[j + kx].hi, wh[6 + kx], aA[j][1]);
+            }
+    }
+    if (HAS_B) {
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+#pragma unroll
+            for (int kx = 0; kx < 3; ++kx) {
+                aB[j][0] = ffma2(in[j + kx].lo, wl[3 + kx], aB[j][0]);
+                aB[j][1] = ffma2(in[j + kx].hi, wh[3 + kx], aB[j][1]);
+            }
+    }
+    if (HAS_C) {
+        if (c) {
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                float2 cl = dwt::fmul2(in[j].lo, wl[0]), ch = dwt::fmul2(in[j].hi, wh[0]);
+#pragma unroll
+                for (int kx = 1; kx < 3; ++kx) {
+                    cl = ffma2(in[j + kx].lo, wl[kx], cl);
+                    ch = ffma2(in[j + kx].hi, wh[kx], ch);
+                }
+                aC[j][0] = cl;
+                aC[j][1] = ch;
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 2; ++j) aC[j][0] = aC[j][1] = make_float2(0.f, 0.f);
         }
     }
 }
@@ -364,16 +408,18 @@ k_sepconv_mid(const __grid_constant__ CUtensorMap tmX /*3-D (C, W, B*H), box 64 
             const int r_lo = g0 / g.W;
             const int x_off = g0 - r_lo * g.W;                 // the tile's first pixel sits at column x_off of image row r_lo
             const int nr = (x_off + BM - 1) / g.W + 1;         // image rows the tile touches
-            const int y_lo = strip * g.RS;
-            const int y_hi = min(y_lo + g.RS, nr);
+            const int y_lo = strip * DW_RS;
             const int yimg_lo = (r_lo + y_lo) % g.H;           // position of the strip's first output row inside its image
+            // input row i of the strip (i = 0 is the halo row above) has image position (yimg_lo - 1 + i) mod H: zero at i = ib
+            const int ib0 = yimg_lo == 0 ? 1 : g.H - yimg_lo + 1;
+            const int ib = ib0 <= DW_RS + 1 ? ib0 : -1;
             for (int kc = 0; kc < g.kchunks; ++kc) {
                 MP_ADD(w_cmp);
                 mbar_wait(x_full(xs), xph);
                 MP_ADD(w_xf);
                 mbar_wait(a_empty(as), aph ^ 1u);
                 MP_ADD(w_ae);
-                if (active && y_lo < y_hi) {
+                if (active && y_lo < nr) {
                     const uint32_t xt = x_base + xs * XSTAGE;
                     const uint32_t wb = xt + g.x_bytes + (uint32_t)cg * 16u;
                     float2 wl[9], wh[9];
@@ -413,55 +459,27 @@ k_sepconv_mid(const __grid_constant__ CUtensorMap tmX /*3-D (C, W, B*H), box 64 
                             aB[j][0] = aC[j][0]; aB[j][1] = aC[j][1];
                         }
                     };
-                    // yi = position inside its image of the INPUT row being scattered; a row contributes upwards (bottom taps of the
-                    // output row above) only if it is not the first row of its image, downwards only if it is not the last.  The
-                    // rows next to an image boundary take a specialised copy of the scatter (warp-uniform branch), all others the
-                    // full one; the next row's pixels are always in flight while the current row is processed.
-                    int yi = yimg_lo == 0 ? g.H - 1 : yimg_lo - 1;
-                    const int last = g.H - 1;
+                    // A strip always computes DW_RS output rows from DW_RS + 2 staged rows, fully unrolled (rows past the tile's last
+                    // pixel are computed from whatever is staged there and dropped by the p < 128 test in store_row).  ib = which of
+                    // those input rows is the FIRST row of an image (or -1): that row must not feed the output row above it, and the row
+                    // before it must not feed the output row below.  At most one boundary fits into DW_RS + 2 <= H rows.
                     dwt::Px in[4];
                     Raw cur = load_raw(rowaddr);
                     Raw nxt = load_raw(rowaddr + rowpitch);
                     rowaddr += 2u * rowpitch;
-                    // input row y_lo - 1: only its top taps matter (they open output row y_lo)
-                    unpack_raw<RELU_IN>(cur, in);
-                    if (yi != last) scatter_px<false, false, true>(in, wl, wh, aA, aB, aC);
-                    else scatter_px<false, false, false>(in, wl, wh, aA, aB, aC);
-                    rotate();
-                    if (++yi == g.H) yi = 0;
-                    cur = nxt;
-                    nxt = load_raw(rowaddr);
-                    rowaddr += rowpitch;
-                    // input row y_lo: middle taps of row y_lo, top taps of row y_lo + 1
-                    unpack_raw<RELU_IN>(cur, in);
-                    if (yi != last) scatter_px<false, true, true>(in, wl, wh, aA, aB, aC);
-                    else scatter_px<false, true, false>(in, wl, wh, aA, aB, aC);
-                    rotate();
-                    if (++yi == g.H) yi = 0;
-                    cur = nxt;
-                    for (int r = y_lo + 1; r < y_hi; ++r, rowaddr += rowpitch) {
-                        nxt = load_raw(rowaddr);
+#pragma unroll
+                    for (int i = 0; i < DW_RS + 2; ++i) {
                         unpack_raw<RELU_IN>(cur, in);
-                        if (yi == 0) scatter_px<false, true, true>(in, wl, wh, aA, aB, aC);
-                        else if (yi == last) scatter_px<true, true, false>(in, wl, wh, aA, aB, aC);
-                        else scatter_px<true, true, true>(in, wl, wh, aA, aB, aC);
-                        store_row();
-                        rotate();
-                        if (++yi == g.H) yi = 0;
                         cur = nxt;
+                        if (i + 2 < DW_RS + 2) { nxt = load_raw(rowaddr); rowaddr += rowpitch; }
+                        const bool a = i != ib, c = i + 1 != ib;
+                        if (i == 0) scatter_rt<false, false, true>(in, wl, wh, aA, aB, aC, a, c);
+                        else if (i == 1) scatter_rt<false, true, true>(in, wl, wh, aA, aB, aC, a, c);
+                        else if (i <= DW_RS) scatter_rt<true, true, true>(in, wl, wh, aA, aB, aC, a, c);
+                        else scatter_rt<true, false, false>(in, wl, wh, aA, aB, aC, a, c);
+                        if (i >= 2) store_row();
+                        if (i <= DW_RS) rotate();
                     }
-                    // input row y_hi: only its bottom taps matter (they close output row y_hi - 1)
-                    unpack_raw<RELU_IN>(cur, in);
-                    if (yi != 0) {
-#pragma unroll
-                        for (int j = 0; j < 2; ++j)
-#pragma unroll
-                            for (int kx = 0; kx < 3; ++kx) {
-                                aA[j][0] = ffma2(in[j + kx].lo, wl[6 + kx], aA[j][0]);
-                                aA[j][1] = ffma2(in[j + kx].hi, wh[6 + kx], aA[j][1]);
-                            }
-                    }
-                    store_row();
                 }
                 fence_proxy_async_smem();  // make the generic-proxy A-tile stores visible to the tensor core (async proxy)
                 __syncwarp();
@@ -502,8 +520,11 @@ inline int tile_rows(int W) { return (W + BM - 2) / W + 1; }   // most image row
 
 // K, N <= 768 (two N halves), rows narrow enough for one column-pair sweep (W <= 20) and a halo tile that fits its stage
 inline bool supported(int H, int W, int K, int N) {
-    if (K < 64 || K > 768 || (K % 8) || N < 8 || N > 2 * NHALF || (N % 8) || W < 3 || W > 20 || H < 3) return false;
-    return (uint32_t)((tile_rows(W) + 2) * (W + 2) * 128) <= X_TILE_MAX;
+    if (K < 64 || K > 768 || (K % 8) || N < 8 || N > 2 * NHALF || (N % 8) || W < 3 || W > 20 || H < DW_RS + 2) return false;
+    const int cp = (W + 1) / 2, ns = (DW_WARPS * 2) / cp;
+    if (ns < 1 || ns * DW_RS < tile_rows(W)) return false;          // the strips of DW_RS rows must cover every row a tile touches
+    const int rows = (ns * DW_RS > tile_rows(W) ? (tile_rows(W) + DW_RS - 1) / DW_RS * DW_RS : tile_rows(W)) + 2;
+    return (uint32_t)(rows * (W + 2) * 128) <= X_TILE_MAX;
 }
 
 // in [B,H,W,K] (pitch ld_in), dwpad [K/64][9][64] fp32, pointwise weights via tmB192 (box 64 x 192 over Wt[N][Kp]),
@@ -518,11 +539,10 @@ inline int launch(const TmaEncoder &enc, const bf16 *in, const float *dwpad, con
     g.items = g.num_tiles * g.n_halves;
     g.kchunks = (K + CB - 1) / CB;
     g.BWp = W + 2;
-    g.BH = tile_rows(W) + 2;
     g.CP = (W + 1) / 2;
-    g.NS = (DW_WARPS * 2) / g.CP;                  // 16-thread channel-group rows available / column pairs
-    if (g.NS > tile_rows(W)) g.NS = tile_rows(W);
-    g.RS = (tile_rows(W) + g.NS - 1) / g.NS;
+    g.NS = (tile_rows(W) + DW_RS - 1) / DW_RS;     // strips of DW_RS output rows (supported() made sure the depthwise warps can hold them)
+    g.RS = DW_RS;
+    g.BH = g.NS * DW_RS + 2;                       // every strip reads DW_RS + 2 staged rows
     g.relu_out = relu_out;
     g.ldo = ld_out;
     g.x_bytes = (uint32_t)(g.BH * g.BWp * 128);
