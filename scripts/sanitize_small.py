@@ -9,12 +9,21 @@ W = weights.make_weights(1, "calibrated")
 rng = np.random.default_rng(0)
 imgs = [rng.integers(0, 256, (h, w, 3), dtype=np.uint8) for h, w in [(77, 130), (300, 298)]]
 for size in (150, 299):
-    m = engine.Model(W, max_batch=2, input_size=size, precision="bf16", use_graphs=False)
-    y = m.predict_uint8(imgs)
-    x = m.preprocess_uint8(imgs)
-    y2 = m.forward_device(x).cpu().numpy()
-    assert np.array_equal(y, y2)
-    m.close()
+    ref = None
+    # default kernels, then every opt-in kernel variant (tensor-core conv1 is the default on the uint8 route; conv1_tc = 0 makes the
+    # uint8 and float routes bit-identical)
+    for tuning in ({"conv1_tc": 0}, {}, {"fused_midflow": 1}, {"dw_tma_store": 1}, {"fused_sepconv": 0}):
+        m = engine.Model(W, max_batch=2, input_size=size, precision="bf16", use_graphs=False, tuning=tuning)
+        y = m.predict_uint8(imgs)
+        if tuning == {"conv1_tc": 0}:
+            x = m.preprocess_uint8(imgs)
+            y2 = m.forward_device(x).cpu().numpy()
+            assert np.array_equal(y, y2)
+        elif ref is None:
+            ref = y
+        else:
+            assert np.array_equal(y, ref), tuning
+        m.close()
 A = torch.randn((300, 728), device="cuda").to(torch.bfloat16); Wt = torch.randn((728, 728), device="cuda").to(torch.bfloat16)
 b = torch.zeros(728, device="cuda")
 engine.gemm_bf16(A, Wt, b, None, True)
