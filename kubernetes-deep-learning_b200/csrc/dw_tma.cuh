@@ -43,6 +43,9 @@ struct Params {
                      // 0: every thread stores its 8 bytes straight to global memory (3 input stages)
     int stages;      // input ring depth
     uint32_t out_bytes;   // TH * TW * 128: one staged output tile
+#ifdef KDL_MID_PROF
+    int ablate;      // probe builds: 1 = consumers only wait and release, 2 = loads + stores (no arithmetic), 3 = loads + arithmetic (no stores)
+#endif
 };
 
 inline Params make_params(int B, int H, int W, int C, int ld, int relu_in, uint32_t tile_budget = TILE_BUDGET, int max_ns = 3) {
@@ -74,6 +77,9 @@ inline Params make_params(int B, int H, int W, int C, int ld, int relu_in, uint3
     p.tma_store = 0;
     p.stages = STAGES;
     p.out_bytes = (uint32_t)(p.TH * p.TW * 128);
+#ifdef KDL_MID_PROF
+    p.ablate = 0;
+#endif
     return p;
 }
 inline uint32_t smem_bytes(const Params &p) {
@@ -202,6 +208,13 @@ __device__ __forceinline__ void dw_body(const CUtensorMap &tmIn, const CUtensorM
                 const int ty = s % p.nty;
                 const int b = s / p.nty;
                 tc::mbar_wait(empty_bar(stage), phase ^ 1u);
+#ifdef KDL_MID_PROF
+                if (p.ablate == 4 || p.ablate == 6) {   // no loads at all: hand the (stale) stage straight to the consumers
+                    tc::mbar_arrive(full_bar(stage));
+                    if (++stage == NST) { stage = 0; phase ^= 1u; }
+                    continue;
+                }
+#endif
                 tc::mbar_expect_tx(full_bar(stage), p.stage_bytes);
                 const uint32_t dst = base + stage * p.stage_bytes;
                 tma_load_4d(dst, &tmIn, full_bar(stage), ch * CB, tx * p.TW - 1, ty * p.TH - 1, b);
@@ -259,7 +272,34 @@ __device__ __forceinline__ void dw_body(const CUtensorMap &tmIn, const CUtensorM
         const int y_lo = strip * p.RS;                     // tile-relative first output row of the strip
         int y_hi = min(y_lo + p.RS, p.TH);
         y_hi = min(y_hi, p.H - ty * p.TH);                 // clip the last tile row
-        if (active && c < p.C && x0 < p.W && 2 * cp < p.TW && y_lo < y_hi) {
+#ifdef KDL_MID_PROF
+        if ((p.ablate == 2 || p.ablate == 4) && active && c < p.C && x0 < p.W && 2 * cp < p.TW && y_lo < y_hi) {   // the kernel's own store pattern, no arithmetic
+            const bool st1 = (2 * cp + 1 < p.TW) && (x0 + 1 < p.W);
+            bf16 *o = out + (((size_t)b * p.H + (size_t)ty * p.TH + y_lo) * p.W + x0) * p.ld + c;
+            const size_t orow = (size_t)p.W * p.ld;
+            const uint2 v = make_uint2((uint32_t)ti, (uint32_t)c);
+            for (int r = y_lo; r < y_hi; ++r, o += orow) {
+                st_stream(o, v);
+                if (st1) st_stream(o + p.ld, v);
+            }
+        }
+        if (p.ablate == 5 || p.ablate == 6) {   // 16-byte stores: 8 lanes cover one pixel's 128 bytes, a warp four adjacent pixels
+            const int npx = min(p.TH, p.H - ty * p.TH) * p.TW;           // pixels of this tile (the tile's rows are TW wide)
+            const int l8 = lane & 7, lp = lane >> 3;
+            const uint4 v = make_uint4((uint32_t)ti, (uint32_t)lane, 3u, 4u);
+            for (int q = warp * 4 + lp; q < npx; q += n_cwarps * 4) {
+                const int yy = q / p.TW, xx = q - yy * p.TW;
+                if (tx * p.TW + xx >= p.W || ch * CB + l8 * 8 >= p.C) continue;
+                bf16 *o = out + (((size_t)b * p.H + (size_t)ty * p.TH + yy) * p.W + tx * p.TW + xx) * p.ld + ch * CB + l8 * 8;
+                *reinterpret_cast<uint4 *>(o) = v;
+            }
+        }
+        const bool ablate_skip = p.ablate == 1 || p.ablate == 2 || p.ablate >= 4;
+        const bool ablate_nostore = p.ablate == 3;
+#else
+        constexpr bool ablate_skip = false, ablate_nostore = false;
+#endif
+        if (!ablate_skip && active && c < p.C && x0 < p.W && 2 * cp < p.TW && y_lo < y_hi) {
             const uint32_t tile = base + stage * p.stage_bytes;
             const uint32_t wb = tile + p.tile_bytes + (uint32_t)cg * 16u;
             float2 wl[9], wh[9];
@@ -285,6 +325,7 @@ __device__ __forceinline__ void dw_body(const CUtensorMap &tmIn, const CUtensorM
                 uint2 v0, v1;
                 v0.x = tc::pack_bf16(aA[0][0].x, aA[0][0].y); v0.y = tc::pack_bf16(aA[0][1].x, aA[0][1].y);
                 v1.x = tc::pack_bf16(aA[1][0].x, aA[1][0].y); v1.y = tc::pack_bf16(aA[1][1].x, aA[1][1].y);
+                if (ablate_nostore && (v0.x ^ v1.y) != 0x7fc12345u) return;   // arithmetic kept alive, (practically) never stored
                 if (via_smem) {
                     asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(so), "r"(v0.x), "r"(v0.y) : "memory");
                     if (st1) asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(so + 128u), "r"(v1.x), "r"(v1.y) : "memory");
@@ -379,10 +420,16 @@ inline bool encode_output_map(const tc::TmaEncoder &enc, CUtensorMap *tm, void *
                   CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+#ifdef KDL_MID_PROF
+static int g_dw_ablate = 0;
+#endif
 inline int launch(const tc::TmaEncoder &enc, const bf16 *in, const float *wpad, bf16 *out, int B, int H, int W, int C, int ld,
                   int relu_in, cudaStream_t st, char *err, int rev = 0, int tma_store = 0) {
     Params p = make_params(B, H, W, C, ld, relu_in);
     p.rev = rev;
+#ifdef KDL_MID_PROF
+    p.ablate = g_dw_ablate;
+#endif
     if (tma_store && p.TW <= 256 && p.TH <= 256) {
         p.tma_store = 1;
         p.stages = 2;

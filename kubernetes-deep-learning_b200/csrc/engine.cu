@@ -1338,4 +1338,91 @@ extern "C" int kdl_corun_probe(int B, int iters, float *out_us /*[3]*/) {
     cudaStreamDestroy(s1); cudaStreamDestroy(s2);
     return e == cudaSuccess ? 0 : -2;
 }
+
+// Probe: does a chunk-major activation layout ([C/64][B][H][W][64], every 19x19x64 tile one contiguous 46 KB run) move the depthwise
+// kernel closer to the HBM roofline than the pixel-major pitch-768 layout (128-byte pieces 1536 bytes apart)?  Same kernel, same
+// bytes: (a) B images of 728 channels at pitch 768, (b) 12*B "images" of 64 channels at pitch 64.  out_us[0..1].
+__global__ void k_probe_fill(unsigned short *p, size_t n, unsigned seed, float scale) {   // pseudo-random bf16 in (-scale, scale)
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        unsigned h = (unsigned)i * 2654435761u + seed;
+        h ^= h >> 15; h *= 2246822519u; h ^= h >> 13;
+        const float v = ((float)(h & 0xffff) / 32768.f - 1.f) * scale;
+        p[i] = (unsigned short)(__float_as_uint(v) >> 16);
+    }
+}
+__global__ void k_probe_fill_f32(float *p, size_t n, unsigned seed, float scale) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        unsigned h = (unsigned)i * 2654435761u + seed;
+        h ^= h >> 15; h *= 2246822519u; h ^= h >> 13;
+        p[i] = ((float)(h & 0xffff) / 32768.f - 1.f) * scale;
+    }
+}
+static int g_probe_random = 0;
+extern "C" void kdl_layout_probe_data(int random) { g_probe_random = random; }
+extern "C" void kdl_dw_ablate(int mode) { kdl::dwt::g_dw_ablate = mode; }
+extern "C" int kdl_layout_probe(int B, int iters, float *out_us /*[6]*/) {
+    using namespace kdl;
+    char err[512];
+    tc::TmaEncoder enc;
+    enc.init();
+    if (!enc.ok() || dwt::configure(err) || tc::configure(err)) return -2;
+    const int H = 19, LD = 768, C = 728, M = B * H * H;
+    const size_t elems = (size_t)B * H * H * LD;
+    bf16 *X[2], *T[2], *Wt;
+    float *wpad, *bias;
+    for (int i = 0; i < 2; ++i) {
+        cudaMalloc(&X[i], elems * 2 + 65536); cudaMalloc(&T[i], elems * 2 + 65536);
+        cudaMemset(X[i], 0x3c, elems * 2); cudaMemset(T[i], 0, elems * 2);
+    }
+    cudaMalloc(&wpad, 12 * 9 * 64 * 4); cudaMemset(wpad, 0, 12 * 9 * 64 * 4);
+    cudaMalloc(&Wt, (size_t)768 * 768 * 2); cudaMemset(Wt, 0, (size_t)768 * 768 * 2);
+    cudaMalloc(&bias, 768 * 4); cudaMemset(bias, 0, 768 * 4);
+    if (g_probe_random) {   // realistic operands: data-dependent power is part of what a kernel costs inside the forward pass
+        for (int i = 0; i < 2; ++i) {
+            k_probe_fill<<<592, 256>>>((unsigned short *)X[i], elems, 17u + i, 1.f);
+            k_probe_fill<<<592, 256>>>((unsigned short *)T[i], elems, 91u + i, 1.f);
+        }
+        k_probe_fill<<<592, 256>>>((unsigned short *)Wt, (size_t)768 * 768, 5u, 0.05f);
+        k_probe_fill_f32<<<64, 256>>>(wpad, 12 * 9 * 64, 3u, 0.3f);
+        k_probe_fill_f32<<<4, 256>>>(bias, 768, 7u, 0.1f);
+        cudaDeviceSynchronize();
+    }
+    CUtensorMap tmB;
+    enc.encode_2d(&tmB, Wt, C, C, 768 * 2, tc::BLOCK_K, tc::BLOCK_N, 128);
+    cudaStream_t s1;
+    cudaStreamCreateWithFlags(&s1, cudaStreamNonBlocking);
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    int rc = 0;
+    // 0: dw, pixel-major  1: dw, chunk-major  2: GEMM alone (two buffer pairs)  3: dw -> GEMM chain as in the middle flow, serpentine
+    // 4: the same chain, every kernel forwards  5: GEMM alone, same buffers every time (A partly L2-resident)
+    for (int mode = 0; mode < 6; ++mode) {
+        int rev = 0;
+        for (int w = 0; w < 2 + iters; ++w) {
+            if (w == 2) { cudaDeviceSynchronize(); cudaEventRecord(e0, s1); }
+            const int h = w & 1;
+            if (mode == 0) rc |= dwt::launch(enc, X[h], wpad, T[h], B, H, H, C, LD, 0, s1, err);
+            else if (mode == 1) rc |= dwt::launch(enc, X[h], wpad, T[h], B * 12, H, H, 64, 64, 0, s1, err);
+            else if (mode == 2) rc |= tc::launch_gemm(enc, T[h], &tmB, bias, nullptr, X[h], M, C, C, 1, s1, err, LD, LD);
+            else if (mode == 5) rc |= tc::launch_gemm(enc, T[0], &tmB, bias, nullptr, X[0], M, C, C, 1, s1, err, LD, LD);
+            else {
+                const bool serp = mode == 3;
+                if (serp) rev ^= 1;
+                rc |= dwt::launch(enc, X[h], wpad, T[h], B, H, H, C, LD, 0, s1, err, rev);
+                if (serp) rev ^= 1;
+                rc |= tc::launch_gemm(enc, T[h], &tmB, bias, nullptr, X[h ^ 1], M, C, C, 1, s1, err, LD, LD, nullptr, rev);
+            }
+        }
+        cudaEventRecord(e1, s1);
+        cudaEventSynchronize(e1);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        out_us[mode] = ms * 1e3f / iters;
+    }
+    cudaError_t e = cudaDeviceSynchronize();
+    for (int i = 0; i < 2; ++i) { cudaFree(X[i]); cudaFree(T[i]); }
+    cudaFree(wpad); cudaFree(Wt); cudaFree(bias);
+    cudaStreamDestroy(s1);
+    return (e == cudaSuccess && rc == 0) ? 0 : -2;
+}
 #endif
