@@ -135,4 +135,32 @@ __device__ __forceinline__ float scale_px(uint8_t v) {
     return __fsub_rn(__fdiv_rn((float)v, 127.5f), 1.0f);
 }
 
+
+#ifdef KDL_MID_PROF
+// probe builds: effective SM clock while a kernel runs.  CTA 0's first thread records clock64 and %globaltimer when it starts and when
+// it ends; slot 0 = pointwise GEMM, 1 = depthwise.  [slot][0..3] = cycles, nanoseconds, launches seen, reserved
+static __device__ unsigned long long g_clk_meter[4][4];
+struct ClkMeter {
+    long long c0;
+    unsigned long long t0;
+    int slot;
+    bool on;
+    __device__ __forceinline__ ClkMeter(int s) : slot(s), on(blockIdx.x == 0 && threadIdx.x == 0) {
+        if (on) {
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+            c0 = clock64();
+        }
+    }
+    __device__ __forceinline__ void stop() {
+        if (on) {
+            const long long c1 = clock64();
+            unsigned long long t1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            g_clk_meter[slot][0] += (unsigned long long)(c1 - c0);
+            g_clk_meter[slot][1] += t1 - t0;
+            g_clk_meter[slot][2] += 1;
+        }
+    }
+};
+#endif
 }  // namespace kdl

@@ -194,6 +194,9 @@ __device__ __forceinline__ void dw_body(const CUtensorMap &tmIn, const CUtensorM
     __syncthreads();
     pdl_launch_dependents();
     pdl_wait();
+#ifdef KDL_MID_PROF
+    ClkMeter clk_meter(1);   // thread 0 is a consumer: it runs to the end of the tile loop
+#endif
 
     if (warp == n_cwarps) {
         // ================= producer warp =================
@@ -369,6 +372,9 @@ __device__ __forceinline__ void dw_body(const CUtensorMap &tmIn, const CUtensorM
         }
         if (++stage == NST) { stage = 0; phase ^= 1u; }
     }
+#ifdef KDL_MID_PROF
+    clk_meter.stop();
+#endif
 }
 
 template <bool RELU, bool TMAS = false>

@@ -1360,6 +1360,16 @@ __global__ void k_probe_fill_f32(float *p, size_t n, unsigned seed, float scale)
 static int g_probe_random = 0;
 extern "C" void kdl_layout_probe_data(int random) { g_probe_random = random; }
 extern "C" void kdl_dw_ablate(int mode) { kdl::dwt::g_dw_ablate = mode; }
+// effective SM clock while the GEMM (slot 0) / depthwise (slot 1) / conv2 (slot 2) kernels ran since the last reset: [slot][cycles, ns, launches, -]
+extern "C" int kdl_clk_meter_read(unsigned long long *out /*[16]*/, int reset) {
+    cudaDeviceSynchronize();
+    if (cudaMemcpyFromSymbol(out, kdl::g_clk_meter, sizeof(unsigned long long) * 16) != cudaSuccess) return -2;
+    if (reset) {
+        unsigned long long z[16] = {0};
+        if (cudaMemcpyToSymbol(kdl::g_clk_meter, z, sizeof z) != cudaSuccess) return -2;
+    }
+    return 0;
+}
 extern "C" int kdl_layout_probe(int B, int iters, float *out_us /*[6]*/) {
     using namespace kdl;
     char err[512];

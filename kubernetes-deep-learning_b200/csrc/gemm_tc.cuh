@@ -331,6 +331,9 @@ __device__ __forceinline__ void gemm_tc_body(const CUtensorMap &tmA, const CUten
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
     pdl_launch_dependents();
     pdl_wait();  // everything above overlapped the previous kernel; global memory is touched only from here on
+#ifdef KDL_MID_PROF
+    ClkMeter clk_meter(CONV ? 2 : 0);
+#endif
 
     if (warp == 0) {
         // ================= TMA producer =================
@@ -539,6 +542,9 @@ __device__ __forceinline__ void gemm_tc_body(const CUtensorMap &tmA, const CUten
     }
     tc_fence_before();
     __syncthreads();
+#ifdef KDL_MID_PROF
+    clk_meter.stop();
+#endif
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, C::TMEM_COLS);

@@ -79,6 +79,12 @@ template <int ORDER> __global__ void __launch_bounds__(512, 1) k_scatter(float *
                 for (int r = 0; r < 3; ++r)
 #pragma unroll
                     for (int kx = 0; kx < 3; ++kx) {
+                        if (ORDER == 3) {   // the same MACs as scalar FFMA
+                            a[r][j][0].x = fmaf(in_lo[j + kx].x, wl[3 * r + kx].x, a[r][j][0].x);
+                            a[r][j][0].y = fmaf(in_lo[j + kx].y, wl[3 * r + kx].y, a[r][j][0].y);
+                            a[r][j][1].x = fmaf(in_hi[j + kx].x, wh[3 * r + kx].x, a[r][j][1].x);
+                            a[r][j][1].y = fmaf(in_hi[j + kx].y, wh[3 * r + kx].y, a[r][j][1].y);
+                        }
                         if (ORDER != 0) continue;
                         a[r][j][0] = ffma2(in_lo[j + kx], wl[3 * r + kx], a[r][j][0]);
                         a[r][j][1] = ffma2(in_hi[j + kx], wh[3 * r + kx], a[r][j][1]);
@@ -163,13 +169,14 @@ int main() {
         cudaMemset(w, 0, 64 * 4);
         cudaEvent_t e0, e1;
         cudaEventCreate(&e0); cudaEventCreate(&e1);
-        for (int order = 0; order < 3; ++order)
+        for (int order = 0; order < 4; ++order)
         for (int warps : {4, 16}) {
             const int trips = 4000;
             auto go = [&](int tr) {
                 if (order == 0) k_scatter<0><<<sms, warps * 32>>>(d, tr, w);
                 if (order == 1) k_scatter<1><<<sms, warps * 32>>>(d, tr, w);
                 if (order == 2) k_scatter<2><<<sms, warps * 32>>>(d, tr, w);
+                if (order == 3) k_scatter<3><<<sms, warps * 32>>>(d, tr, w);
             };
             go(10);
             cudaEventRecord(e0);
@@ -181,7 +188,7 @@ int main() {
             int clk_khz;
             cudaDeviceGetAttribute(&clk_khz, cudaDevAttrClockRate, 0);
             const double macs = 72.0 * 16 * (double)trips * warps * 32;
-            const char *on[] = {"depthwise scatter pattern, compiler order", "scatter grouped by input operand", "scatter grouped by weight operand"};
+            const char *on[] = {"depthwise scatter pattern, compiler order", "scatter grouped by input operand", "scatter grouped by weight operand", "scatter as scalar FFMA, compiler order"};
             printf("%-42s %2d warps/SM: %7.1f MAC/clk/SM  (%.2f ms)\n", on[order], warps, macs / (ms * 1e-3 * clk_khz * 1e3), ms);
         }
     }
