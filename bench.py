@@ -438,6 +438,23 @@ def main():
         configs["mixed_size_e2e_latency"] = dict(mixed, api="kdl_predict_u8_host: pinned host pixels of mixed sizes (64..2048)^2 -> "
                                                  "H2D -> fused resize+scale -> Xception -> D2H logits")
         configs["latency_b1"] = latency
+        # the same step held for seconds: after ~0.5 s the GPU sits at its power limit and the SM clock drops (scripts/clk_meter.py),
+        # which the K timed steps above end too early to see; device-resident inputs, wall clock around synchronised groups of 20
+        Tsus = 4.0
+        o_s = torch.empty((B, 10), dtype=torch.float32, device="cuda")
+        time.sleep(1.0)
+        smp = ClockSampler(local_rank)
+        smp.start()
+        t0 = time.perf_counter()
+        n_s = 0
+        while time.perf_counter() - t0 < Tsus:
+            for i in range(20):
+                model.predict_packed_device(d_src[i % NSETS], packs[i % NSETS], o_s)
+            torch.cuda.synchronize()
+            n_s += 20
+        el = time.perf_counter() - t0
+        configs["sustained"] = {"workload": f"the N=1 workload (batch {B}) back to back for {Tsus:.0f} s, device-resident", "value": B * n_s / el,
+                                "unit": UNIT, "ms_per_step": el / n_s * 1e3, "steps": n_s, "clocks": smp.stop()}
     if strong is not None and rank == 0:
         configs = configs if configs is not None else {}
         configs["strong_b1024"] = strong
