@@ -207,8 +207,11 @@ int main(int argc, char **argv) {
     if (argc < 2) return 0;   // the pair section below hung once on a B200 (no trap fired); run it only on request: mma_rate pair
     printf("\ncta_group::2 (M = 256 over a CTA pair; per SM: 128 rows of A + N/2 rows of B)\n");
     cudaFuncSetAttribute(k_probe_pair, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    for (int N : {256, 128}) {
+    const bool quiet_only = argc >= 2 && argv[1][0] == 'q';   // "q": no competing ld.shared warps, more N values (the safe subset)
+    for (int N : {256, 224, 192, 160, 128, 96, 64}) {
+        if (!quiet_only && N != 256 && N != 128) continue;
         for (int lw : {0, 4, 16}) {
+            if (quiet_only && lw != 0) continue;
             cudaMemset(d, 0, sizeof(Res) * sms);
             k_probe_pair<<<sms & ~1, 32 * (2 + lw), smem>>>(N, iters, lw, d);
             cudaError_t e = cudaDeviceSynchronize();
