@@ -367,13 +367,16 @@ def main():
                 "unit": "TFLOP/s"}
     else:
         roof = {"bound": "hbm", "achieved": dom["achieved_gbs"], "peak": peaks["hbm_gbs"], "unit": "GB/s"}
-    traffic = None
+    # `traffic` is the contract's number (DRAM bytes read + written per launch, from the committed ncu --set full capture) or null;
+    # which launch it was taken on, its algorithmic bytes and the source file ride along in `traffic_detail`
+    traffic, traffic_detail = None, None
     tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
     if os.path.exists(tpath):
         tj = json.load(open(tpath))
         if dom["kernel"] in tj:
-            traffic = dict(tj[dom["kernel"]], source=tj.get("_source"))
-    roof.update({"frac": roof["achieved"] / roof["peak"], "traffic": traffic, "kernel": dom["kernel"],
+            traffic_detail = dict(tj[dom["kernel"]], unit="bytes per launch", source=tj.get("_source"))
+            traffic = traffic_detail.get("traffic_bytes_per_launch")
+    roof.update({"frac": roof["achieved"] / roof["peak"], "traffic": traffic, "traffic_detail": traffic_detail, "kernel": dom["kernel"],
                  "launches_per_step": dom["launches_per_step"], "avg_launch_ms": dom["ms_per_step"] / max(dom["launches_per_step"], 1),
                  "peak_source": peaks["_source"] + (" sustained bf16" if dom["bound"] == "tensor" else " copy bandwidth"),
                  "timing": f"cuda events around each launch over {K} steps (separate pass right after the timed region)"})
