@@ -61,9 +61,12 @@ typedef struct KdlTuning {
                                     rows its producer wrote last (activations exceed the 126 MB L2 at large batch) */
     int32_t conv2_shifted_taps;  /* !=0: block1_conv2 as 9 shifted TMA boxes per tile instead of the staged halo (default 0) */
     int32_t fused_sepconv;       /* !=0 (default): blocks 2-3 run the fused depthwise+pointwise kernel */
-    int32_t fused_midflow;       /* !=0: 728 -> 728 layers at 19 x 19 (middle flow, block13_sepconv1) run the fused depthwise+pointwise
-                                    kernel with flat-pixel tiles (sepconv_mid.cuh).  Default 0: it is bit-identical but measured
-                                    slower than k_dw_tma + k_gemm_tc on a B200 (DESIGN.md §4 has the cycle breakdown) */
+    int32_t fused_midflow;       /* !=0: 728 -> 728 layers at 19 x 19 (middle flow, block13_sepconv1) run a fused depthwise+pointwise
+                                    kernel with flat-pixel tiles: 1 = one CTA per (tile, N half), the depthwise tile computed twice
+                                    (sepconv_mid.cuh); 2 = a CTA pair (cluster of 2) per tile, the depthwise chunks split between
+                                    the two CTAs and exchanged through distributed shared memory (sepconv_pair.cuh).  Default 0:
+                                    both are bit-identical to but measured slower than k_dw_tma + k_gemm_tc on a B200
+                                    (DESIGN.md §4 has the cycle breakdowns) */
     int32_t conv1_tc;            /* !=0 (default): block1_conv1 of the uint8 path runs as a tcgen05 implicit GEMM on the raw pixel
                                     values (exact in bf16; x/127.5-1 folded into bf16 weights + fp32 bias).  0: the CUDA-core kernel
                                     with fp32 weights (always used for float inputs and the fp32 path).  The ONE switch that

@@ -13,7 +13,7 @@ from kdl_b200 import _lib, engine, weights
 
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 256
 W = weights.make_weights(1, "calibrated")
-m = engine.Model(W, max_batch=B, precision="bf16", use_graphs=False, tuning={"fused_midflow": 1})
+m = engine.Model(W, max_batch=B, precision="bf16", use_graphs=False, tuning={"fused_midflow": int(os.environ.get("KDL_MIDFLOW", "1"))})
 rng = np.random.default_rng(0)
 pk = engine.PackedImages([rng.integers(0, 256, (299, 299, 3), dtype=np.uint8) for _ in range(B)])
 d = pk.host.cuda()
