@@ -64,8 +64,9 @@ typedef struct KdlTuning {
     int32_t fused_midflow;       /* !=0: 728 -> 728 layers at 19 x 19 (middle flow, block13_sepconv1) run a fused depthwise+pointwise
                                     kernel with flat-pixel tiles: 1 = one CTA per (tile, N half), the depthwise tile computed twice
                                     (sepconv_mid.cuh); 2 = a CTA pair (cluster of 2) per tile, the depthwise chunks split between
-                                    the two CTAs and exchanged through distributed shared memory (sepconv_pair.cuh).  Default 0:
-                                    both are bit-identical to but measured slower than k_dw_tma + k_gemm_tc on a B200
+                                    the two CTAs and exchanged through distributed shared memory (sepconv_pair.cuh); 3 = a cluster
+                                    of three, 256 output columns and two TMEM accumulators per CTA (sepconv_trio.cuh).  Default 0:
+                                    all three are bit-identical to but measured slower than k_dw_tma + k_gemm_tc on a B200
                                     (DESIGN.md §4 has the cycle breakdowns) */
     int32_t conv1_tc;            /* !=0 (default): block1_conv1 of the uint8 path runs as a tcgen05 implicit GEMM on the raw pixel
                                     values (exact in bf16; x/127.5-1 folded into bf16 weights + fp32 bias).  0: the CUDA-core kernel

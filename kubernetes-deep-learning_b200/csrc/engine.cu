@@ -22,6 +22,7 @@
 #include "sepconv_tc.cuh"
 #include "sepconv_mid.cuh"
 #include "sepconv_pair.cuh"
+#include "sepconv_trio.cuh"
 #include "kernels.cuh"
 
 using namespace kdl;
@@ -356,13 +357,18 @@ template <typename T> struct Runner {
     }
     // fused_midflow == 2: the CTA-pair kernel (sepconv_pair.cuh) where it applies, k_sepconv_mid elsewhere
     bool use_pair(int si, int H) const { return m->tune.fused_midflow == 2 && sepp::supported(H, H, m->pw[si].K, m->pw[si].N); }
+    // fused_midflow == 3: clusters of three CTAs, 256 output columns each (sepconv_trio.cuh)
+    bool use_trio(int si, int H) const { return m->tune.fused_midflow == 3 && sep3::supported(H, H, m->pw[si].K, m->pw[si].N); }
     int sepconv_mid(const T *in, int si, const T *resid, T *out, int H, int relu_in, int relu_out) {
         const GemmW &g = m->pw[si];
         const double px = (double)B * H * H;
         prof_open(m, st, PC_SEPMID, 2.0 * px * (9.0 * g.K + (double)g.K * g.N),
                   (px * g.K + px * g.N * (resid ? 2 : 1) + (double)g.K * g.N) * 2.0 + 36.0 * g.K, "sepmid H=%d K=%d N=%d", H, g.K, g.N);
         no_flip();
-        int rc = use_pair(si, H)
+        int rc = use_trio(si, H)
+                     ? sep3::launch(m->tma, (const bf16 *)in, m->dwpad[si], &g.tmB, g.bias, (const bf16 *)resid, (bf16 *)out, B, H, H, g.K, g.N,
+                                    ld(g.K), ld(g.N), relu_in, relu_out, st, m->err)
+                 : use_pair(si, H)
                      ? sepp::launch(m->tma, (const bf16 *)in, m->dwpad[si], &g.tmB192, g.bias, (const bf16 *)resid, (bf16 *)out, B, H, H, g.K,
                                     g.N, ld(g.K), ld(g.N), relu_in, relu_out, st, m->err)
                      : sepm::launch(m->tma, (const bf16 *)in, m->dwpad[si], &g.tmB192, g.bias, (const bf16 *)resid, (bf16 *)out, B, H, H, g.K,
@@ -817,7 +823,7 @@ extern "C" int kdl_create(const KdlConfig *cfg, KdlModel **out) {
     }
     CKM(cudaStreamCreateWithFlags(&m->own_stream, cudaStreamNonBlocking));
     m->tune = default_tuning();
-    if ((rc = tc::configure(m->err)) != KDL_OK || (rc = convtc::configure(m->err)) != KDL_OK || (rc = dwt::configure(m->err)) != KDL_OK || (rc = poolt::configure(m->err)) != KDL_OK || (rc = sepc::configure(m->err)) != KDL_OK || (rc = sepm::configure(m->err)) != KDL_OK || (rc = sepp::configure(m->err)) != KDL_OK || (rc = c1tc::configure(m->err)) != KDL_OK) { set_err(g_err, "%s", m->err); kdl_destroy(m); return rc; }
+    if ((rc = tc::configure(m->err)) != KDL_OK || (rc = convtc::configure(m->err)) != KDL_OK || (rc = dwt::configure(m->err)) != KDL_OK || (rc = poolt::configure(m->err)) != KDL_OK || (rc = sepc::configure(m->err)) != KDL_OK || (rc = sepm::configure(m->err)) != KDL_OK || (rc = sepp::configure(m->err)) != KDL_OK || (rc = sep3::configure(m->err)) != KDL_OK || (rc = c1tc::configure(m->err)) != KDL_OK) { set_err(g_err, "%s", m->err); kdl_destroy(m); return rc; }
 #undef CKM
     *out = m;
     return KDL_OK;
@@ -870,7 +876,7 @@ extern "C" int kdl_set_tuning(KdlModel *m, const KdlTuning *t) {
 extern "C" const char *kdl_last_error(const KdlModel *m) { return m ? m->err : g_err; }
 extern "C" int kdl_last_launch_count(const KdlModel *m) { return m ? m->launches : 0; }
 extern "C" const char *kdl_version(void) {
-    return "kdl 0.3 sm_100a: k_resize k_conv1 k_conv1_tc k_conv3x3_tc k_dw_tma k_sepconv_tc k_sepconv_mid k_sepconv_pair k_pool_tma k_gemm_tc(tcgen05/TMEM/TMA) k_gap_partial k_head_finish";
+    return "kdl 0.3 sm_100a: k_resize k_conv1 k_conv1_tc k_conv3x3_tc k_dw_tma k_sepconv_tc k_sepconv_mid k_sepconv_pair k_sepconv_trio k_pool_tma k_gemm_tc(tcgen05/TMEM/TMA) k_gap_partial k_head_finish";
 }
 
 // ---------------------------------------------------------------------------------------------------

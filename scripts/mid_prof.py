@@ -29,8 +29,12 @@ a = np.frombuffer(buf, dtype=np.uint64).reshape(n, 32).astype(np.float64)
 names = ["prod wait x_empty", "prod wait b_empty", "prod issue", "mma wait tempty", "mma wait a_full", "mma wait b_full", "mma issue",
          "epi wait tfull", "epi work", "dw6 wait x_full", "dw6 wait a_empty", "dw6 compute", "dw15 wait x_full", "dw15 wait a_empty",
          "dw15 compute"]
-items = -(-(B * 361) // 128) * 2 / n
-print(f"batch {B}: {items:.2f} items per CTA (last launch: block13_sepconv1 728->728 @19x19)")
+mode = os.environ.get("KDL_MIDFLOW", "1")
+act = a[:, 6] > 0                      # CTAs that ran (a cluster launch may use fewer than 148)
+a = a[act]
+tiles = -(-(B * 361) // 128)
+items = tiles * 2 / 148 if mode == "1" else tiles / (act.sum() / (2 if mode == "2" else 3))
+print(f"batch {B}: {int(act.sum())} CTAs ran, {items:.2f} items per CTA (last launch: block13_sepconv1 728->728 @19x19)")
 for i, nm in enumerate(names):
     print(f"{nm:22s} mean {a[:, i].mean():10.0f} clk   per item {a[:, i].mean() / items:8.0f}   min {a[:, i].min():9.0f} max {a[:, i].max():9.0f}")
 m.close()

@@ -12,7 +12,8 @@ rng = np.random.default_rng(0)
 pk = engine.PackedImages([rng.integers(0, 256, (299, 299, 3), dtype=np.uint8) for _ in range(B)])
 d = pk.host.cuda()
 outs = {}
-for name, tun in (("default", {}), ("fused_midflow=1", {"fused_midflow": 1}), ("fused_midflow=2 (pair)", {"fused_midflow": 2})):
+for name, tun in (("default", {}), ("fused_midflow=1", {"fused_midflow": 1}), ("fused_midflow=2 (pair)", {"fused_midflow": 2}),
+                  ("fused_midflow=3 (trio)", {"fused_midflow": 3})):
     m = engine.Model(W, max_batch=B, precision="bf16", tuning=tun)
     out = torch.empty((B, 10), device="cuda")
     for _ in range(3):

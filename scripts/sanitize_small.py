@@ -12,7 +12,7 @@ for size in (150, 299):
     ref = None
     # default kernels, then every opt-in kernel variant (tensor-core conv1 is the default on the uint8 route; conv1_tc = 0 makes the
     # uint8 and float routes bit-identical)
-    for tuning in ({"conv1_tc": 0}, {}, {"fused_midflow": 1}, {"fused_midflow": 2}, {"dw_tma_store": 1}, {"fused_sepconv": 0}):
+    for tuning in ({"conv1_tc": 0}, {}, {"fused_midflow": 1}, {"fused_midflow": 2}, {"fused_midflow": 3}, {"dw_tma_store": 1}, {"fused_sepconv": 0}):
         m = engine.Model(W, max_batch=2, input_size=size, precision="bf16", use_graphs=False, tuning=tuning)
         y = m.predict_uint8(imgs)
         if tuning == {"conv1_tc": 0}:

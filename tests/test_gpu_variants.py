@@ -29,7 +29,7 @@ def test_kernel_variants_are_bit_identical():
     base = _logits({}, W, u8)
     assert len({tuple(r) for r in base.round(3).tolist()}) == 5          # five pictures, five different answers
     for tuning in ({"fused_sepconv": 0}, {"conv2_shifted_taps": 1}, {"pdl_max_batch": 1 << 20}, {"pdl_max_batch": 0},
-                   {"serpentine": 0}, {"dw_tma_store": 1}, {"fused_midflow": 1}, {"fused_midflow": 2}, {"fused_midflow": 0, "fused_sepconv": 0}):
+                   {"serpentine": 0}, {"dw_tma_store": 1}, {"fused_midflow": 1}, {"fused_midflow": 2}, {"fused_midflow": 3}, {"fused_midflow": 0, "fused_sepconv": 0}):
         got = _logits(tuning, W, u8)
         np.testing.assert_array_equal(got, base, err_msg=str(tuning))
 
@@ -140,8 +140,8 @@ def test_metric_batch_256_is_position_independent_and_matches_small_batches():
         np.testing.assert_array_equal(big[pos], small[i], err_msg=f"position {pos} image {i}")
     np.testing.assert_array_equal(again, big)
     # the opt-in fused middle-flow kernels (flat-pixel tiles, all 722 tiles at this batch; 1 = one CTA per N half,
-    # 2 = CTA pairs sharing the depthwise tile through distributed shared memory) compute the same bits
-    for mode in (1, 2):
+    # 2 / 3 = clusters of two / three CTAs sharing the depthwise tile through distributed shared memory) compute the same bits
+    for mode in (1, 2, 3):
         mf = engine.Model(W, max_batch=256, precision="bf16", tuning={"fused_midflow": mode})
         try:
             np.testing.assert_array_equal(mf.predict_uint8([srcs[i] for i in order]), big, err_msg=f"fused_midflow={mode}")
